@@ -1,0 +1,161 @@
+/*
+ * nfi_b200 -- C ABI of the B200-native (sm_100a) volume-rendering hot path of nerf-from-image.
+ *
+ * The reference has no FFI: its boundary is the set of Python call signatures in
+ * lib/nerf_utils.py, models/generator.py (TriplanarDecoder.forward, the `sampler` closure) and
+ * run.py::render.  The Python package `nfi_b200` keeps those signatures and binds the entry points
+ * below with ctypes (INTEGRATION.md shows the stub).  Each entry point names the reference code it
+ * replaces (file:line relative to the reference checkout).
+ *
+ * Conventions
+ *   - every pointer is a DEVICE pointer to fp32 data unless stated; the caller owns every buffer,
+ *     including outputs and workspaces; the library allocates nothing and keeps no pointer;
+ *   - `stream` is a cudaStream_t (passed as void*); kernels are launched on it and nothing
+ *     synchronises -- safe under nn.DataParallel (several host threads, one device each);
+ *   - return value 0 = success, negative = NFI_ERR_*; nfi_last_error() gives a thread-local message;
+ *   - rays are indexed (b*H + h)*W + w; samples of a ray are contiguous ([R,S] row-major).
+ */
+#ifndef NFI_B200_H
+#define NFI_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define NFI_VERSION 100
+
+#define NFI_OK 0
+#define NFI_ERR_BAD_ARG (-1)      /* NULL pointer, non-positive size, unsupported combination      */
+#define NFI_ERR_UNSUPPORTED (-2)  /* feat_ch != 32, hidden != 64, n_out > 16, S > 64 ...           */
+#define NFI_ERR_ALIGNMENT (-3)    /* a vector-accessed buffer is not 16-byte aligned               */
+#define NFI_ERR_LAUNCH (-4)       /* cudaGetLastError() after a launch                             */
+
+#define NFI_FEAT_CH 32            /* channels per plane      (models/generator.py:384)             */
+#define NFI_HIDDEN 64             /* decoder hidden width    (models/generator.py:294)             */
+#define NFI_MAX_OUT 16            /* 1 + attention_values (<= 15) or 1 + 3                         */
+#define NFI_MAX_S 64              /* samples per ray per pass (run.py:512 uses 64)                 */
+#define NFI_NEARFAR_WS_BYTES 16384
+
+typedef void* nfi_stream_t;
+
+/* Decoder + heads description.  Weight pointers are the RAW EqualizedLinear tensors; the
+ * 1/sqrt(fan_in) gain (models/stylegan.py:170-177) is applied inside the kernels. */
+typedef struct NfiField {
+  const float* W0;   /* [64, 32]  decoder.net[0].weight */
+  const float* b0;   /* [64]                            */
+  const float* W1;   /* [n_out, 64] decoder.net[2].weight */
+  const float* b1;   /* [n_out]                         */
+  const float* beta;  /* [1] (use_sdf) or NULL           */
+  const float* alpha; /* [1] (use_sdf) or NULL           */
+  int32_t n_out;            /* 1 + attention_values, or 1 + 3 for the plain RGB head */
+  int32_t attention_values; /* A; 0 -> wide-sigmoid RGB head (models/generator.py:665-666) */
+  int32_t use_sdf;          /* 1: Laplace-CDF density (generator.py:629-636); 0: softplus(d-1) */
+  float scene_range;        /* points are divided by this (generator.py:604); 1.0 for raw decoder coords */
+} NfiField;
+
+int nfi_version(void);
+const char* nfi_last_error(void);
+
+/* ---- A1: nerf_utils.get_ray_bundle (lib/nerf_utils.py:28-93) + F.normalize (run.py:196) -------
+ * cam2world [B,16] row-major 4x4.  focal: NULL = orthographic; focal_stride 1 = [B], 0 = one shared
+ * value (the 0-dim focal of eval_kitti_persp.py:948).  center [B,2] or NULL; bbox [B,2,2] or NULL.
+ * normalize != 0 applies x / max(|x|, 1e-12) to the directions.  Outputs [B*H*W, 3]. */
+int nfi_ray_bundle_fwd(const float* cam2world, const float* focal, int focal_stride,
+                       const float* center, const float* bbox, int B, int H, int W, int normalize,
+                       float* origins, float* dirs, nfi_stream_t stream);
+/* Backward: g_origins/g_dirs [R,3] (either may be NULL) -> g_cam2world [B,16], g_focal [B]
+ * (per image even when the focal is shared; both are OVERWRITTEN). */
+int nfi_ray_bundle_bwd(const float* cam2world, const float* focal, int focal_stride,
+                       const float* center, const float* bbox, int B, int H, int W, int normalize,
+                       const float* g_origins, const float* g_dirs, float* g_cam2world,
+                       float* g_focal, nfi_stream_t stream);
+
+/* ---- A2: nerf_utils.compute_near_far_planes (lib/nerf_utils.py:227-275) ------------------------
+ * workspace: NFI_NEARFAR_WS_BYTES bytes; on return (stream order) ((int32_t*)workspace)[0] holds the
+ * number of rays that hit the box -- 0 is the case in which the reference raises (nerf_utils.py:260). */
+int nfi_near_far(const float* origins, const float* dirs, int64_t R, float scene_range,
+                 float* near, float* far, void* workspace, nfi_stream_t stream);
+
+/* ---- A3: nerf_utils.compute_query_points_from_rays (lib/nerf_utils.py:96-122) ------------------
+ * u [R,S] uniforms or NULL; randomize with u == NULL draws Philox4x32-10 numbers from (seed, offset). */
+int nfi_stratified(const float* near, const float* far, const float* u, int64_t R, int S,
+                   int randomize, uint64_t seed, uint64_t offset, float* z, nfi_stream_t stream);
+int nfi_points_fwd(const float* origins, const float* dirs, const float* z, int64_t R, int S,
+                   float* points, nfi_stream_t stream);
+/* g_points [R,S,3] -> g_origins [R,3] = sum_s g, g_dirs [R,3] = sum_s g * z (overwritten). */
+int nfi_points_bwd(const float* g_points, const float* z, int64_t R, int S, float* g_origins,
+                   float* g_dirs, nfi_stream_t stream);
+
+/* ---- layout boundary: StyleGAN2 planes [B, 3*32, Hp, Wp] NCHW (models/generator.py:475-477)
+ *      <-> channels-last [B, 3, Hp, Wp, 32] used by the gather/scatter kernels --------------------- */
+int nfi_planes_to_cl(const float* planes_nchw, int B, int Hp, int Wp, float* planes_cl,
+                     nfi_stream_t stream);
+int nfi_planes_grad_from_cl(const float* g_planes_cl, int B, int Hp, int Wp, float* g_planes_nchw,
+                            nfi_stream_t stream);
+
+/* ---- A4-A6: TriplanarDecoder.forward (models/generator.py:301-331) + sampler heads (:587-681) ----
+ * Sample points are either explicit (`points` [B, n_per_image, 3], S = 1) or implicit
+ * o + d * z (`points` NULL; origins/dirs [B*n_per_image, 3], z [B*n_per_image, S]).
+ * mode 0: heads -> out float4 (sigma, r, g, b) per sample; probs_out optional [.., A] (semantics);
+ * mode 1: raw decoder -> out [.., n_out] (density_or_distance, features), no out-of-box mask.
+ * img_w > 0 (ray mode, image width; n_per_image = H*W with H % 8 == 0, W % 16 == 0) lets a tile be
+ * an 8x16 pixel block at one depth step (texel reuse in L1) instead of 128 consecutive samples.
+ * skip_oob != 0 (fused render): out-of-box samples are written as (0,0,0,0) without any gather --
+ * their sigma is 0, so their colour never reaches the image (lib/nerf_utils.py:143-146). */
+int nfi_field_fwd(const NfiField* field, const float* planes_cl, const float* palette, int B, int Hp,
+                  int Wp, const float* origins, const float* dirs, const float* z,
+                  const float* points, int64_t n_per_image, int S, int mode, int img_w,
+                  int skip_oob, float* out, float* probs_out, nfi_stream_t stream);
+/* Backward.  g_out as `out`.  Accumulating outputs (caller zero-fills): g_planes_cl [B,3,Hp,Wp,32],
+ * g_palette [B,A,3], g_params [64*32 + 64 + n_out*64 + n_out + 2] (W0,b0,W1,b1,beta,alpha).
+ * g_points [.., 3] per sample is overwritten.  Any of them may be NULL (not computed). */
+int nfi_field_bwd(const NfiField* field, const float* planes_cl, const float* palette, int B, int Hp,
+                  int Wp, const float* origins, const float* dirs, const float* z,
+                  const float* points, int64_t n_per_image, int S, int mode, int img_w,
+                  const float* g_out, float* g_planes_cl, float* g_palette, float* g_points,
+                  float* g_params, nfi_stream_t stream);
+
+/* ---- A7: render_volume_density_weights_only (lib/nerf_utils.py:166-182) + EG3D smoothing
+ *      (run.py:266-272, smooth != 0).  sigma is read with stride `sigma_stride` floats. ----------- */
+int nfi_weights_only(const float* sigma, int sigma_stride, const float* dirs, const float* z,
+                     int64_t R, int S, int smooth, float* weights, nfi_stream_t stream);
+/* ---- A8: nerf_utils.sample_pdf (lib/nerf_utils.py:185-224): bins [R,M], weights [R,M-1] ->
+ *      samples [R,n]; u [R,n] or NULL (deterministic linspace); inds_out optional int32 [R,n]. ---- */
+int nfi_sample_pdf(const float* bins, const float* weights, int64_t R, int M, int n, const float* u,
+                   float* samples, int32_t* inds_out, nfi_stream_t stream);
+/* A7 + smoothing + A8 in one pass over the coarse samples (run.py:261-281). */
+int nfi_importance(const float* sigma, int sigma_stride, const float* dirs, const float* z_coarse,
+                   int64_t R, int S, const float* u, float* z_fine, nfi_stream_t stream);
+
+/* ---- A10: nerf_utils.render_volume_density (lib/nerf_utils.py:125-163) -------------------------
+ * sigma [R,S], rgb [R,S,3], z [R,S], dirs [R,3]; optional normals [R,S,3], semantics [R,S,n_sem]. */
+int nfi_composite_fwd(const float* sigma, const float* rgb, const float* dirs, const float* z,
+                      const float* normals, const float* semantics, int n_sem, int64_t R, int S,
+                      int white_background, float* rgb_map, float* depth_map, float* mask,
+                      float* normal_map, float* semantic_map, nfi_stream_t stream);
+int nfi_composite_bwd(const float* sigma, const float* rgb, const float* dirs, const float* z,
+                      const float* semantics, int n_sem, int64_t R, int S, int white_background,
+                      const float* g_rgb_map, const float* g_mask, const float* g_semantic_map,
+                      float* g_sigma, float* g_rgb, float* g_dirs, float* g_semantics,
+                      nfi_stream_t stream);
+
+/* ---- A9 + A10 fused: sort/merge of coarse + fine samples (run.py:283-335) and compositing.
+ * coarse/fine: float4 (sigma, r, g, b) [R,S]; perm [R,2S] uint8 (index into cat(coarse, fine)) and
+ * z_sorted [R,2S] are outputs kept for the backward.  cam2world != NULL converts the depth to a
+ * z-buffer depth (eval_kitti_persp.py:221-228); rays_per_image is then needed. ------------------- */
+int nfi_merge_composite_fwd(const float* coarse, const float* fine, const float* z_coarse,
+                            const float* z_fine, const float* dirs, int64_t R, int S,
+                            int white_background, const float* cam2world, int64_t rays_per_image,
+                            float* rgb_map, float* depth_map, float* mask, uint8_t* perm,
+                            float* z_sorted, nfi_stream_t stream);
+int nfi_merge_composite_bwd(const float* coarse, const float* fine, const float* z_sorted,
+                            const uint8_t* perm, const float* dirs, int64_t R, int S,
+                            int white_background, const float* g_rgb_map, const float* g_mask,
+                            float* g_coarse, float* g_fine, nfi_stream_t stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* NFI_B200_H */
