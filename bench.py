@@ -1,0 +1,324 @@
+#!/usr/bin/env python
+"""bench.py -- rays/s (fwd+bwd) of the volume-rendering hot path on N B200s (weak scaling, no
+data-path collective: images are independent).
+
+    python bench.py --gpus N --steps K --warmup W            # this repo's CUDA path
+    python bench.py --impl reference --steps K --warmup W    # CPU arm (oracle port of the reference)
+
+A step = one render forward + backward (loss = the reference's l1 branch, run.py:2236-2238) over
+one batch of synthetic inputs of BASELINE.json config 2: 16 images, 128x128 rays each, 64 coarse +
+64 fine samples per ray, perspective cameras, gradients to planes, attention values, cam2world and
+focal.  Prints ONE JSON line (rank 0).
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+for p in (ROOT, os.path.join(ROOT, "oracle")):
+    if p not in sys.path:
+        sys.path.insert(0, p)
+
+import torch  # noqa: E402
+
+METRIC = "rays/sec (fwd+bwd)"
+UNIT = "rays/s"
+SCENE_RANGE = 1.4
+PLANE_BYTES = 3 * 32 * 256 * 256 * 4          # P, bytes per image
+
+
+def peaks():
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            p = json.load(f)
+        return p, "measured"
+    except Exception:
+        return {"hbm_gbs": 6650.0, "bf16_tflops": 1590.0, "bf16_tflops_sustained": 1400.0}, "fallback"
+
+
+class ClockSampler(threading.Thread):
+    """nvidia-smi clocks / throttle reasons DURING the timed region (B200_PROFILING.md recipe)."""
+    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        super().__init__(daemon=True)
+        self.index, self.rows, self.stop_flag = index, [], False
+        self.proc = None
+
+    def run(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
+                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            for line in self.proc.stdout:
+                if self.stop_flag:
+                    break
+                self.rows.append([c.strip() for c in line.split(",")])
+        except Exception:
+            pass
+
+    def finish(self):
+        self.stop_flag = True
+        if self.proc is not None:
+            self.proc.kill()          # the exact PID we started
+        sm = sorted(int(r[0]) for r in self.rows if r and r[0].isdigit())
+        mx = [int(r[1]) for r in self.rows if len(r) > 1 and r[1].isdigit()]
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = [n for i, n in enumerate(names) if any(len(r) > 2 + i and r[2 + i] == "Active" for r in self.rows)]
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": reasons, "samples": len(sm)}
+
+
+def make_inputs(B, H, W, S, seed_shift=0):
+    """Synthetic config-2 inputs on the CPU: smooth planes, calibrated decoder,
+    random object-centred perspective poses, l1 target."""
+    from nfi_b200 import synth
+    planes = synth.make_planes(B, res=256, seed=1 + seed_shift)
+    fd = synth.make_field(planes, seed=3)
+    pal = synth.make_palette(B, 10, seed=4 + seed_shift)
+    cam, focal = synth.make_cameras(B, seed=2 + seed_shift, perspective=True)
+    target = torch.rand(B, H, W, 3, generator=torch.Generator().manual_seed(7 + seed_shift)) * 2 - 1
+    return planes, fd, pal, cam, focal, target
+
+
+# ---------------------------------------------------------------------------------------------
+# this repo's arm
+# ---------------------------------------------------------------------------------------------
+def run_ours(args):
+    import torch.distributed as dist
+    from nfi_b200 import _lib, decoder, render
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    assert torch.cuda.is_available(), "bench.py (impl=ours) needs a CUDA device; there is no CPU fallback"
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=dev)
+    _lib.lib()
+    B, H, W, S = args.batch, args.res, args.res, 64
+    R = B * H * W
+    planes_h, fd, pal_h, cam_h, focal_h, target_h = make_inputs(B, H, W, S, seed_shift=rank)
+    fld = decoder.Field(*[fd[k].to(dev) for k in ("W0", "b0", "W1", "b1", "beta", "alpha")],
+                        SCENE_RANGE, 10, True)
+
+    def step(planes, pal, cam, focal, target):
+        rgb, depth, mask = render.render_planes(planes, pal, fld, H, W, cam, focal, None, None, S,
+                                                randomize=True, white_background=False)
+        loss = (rgb - target).abs().mean() * B          # run.py:2236-2238 (l1)
+        grads = torch.autograd.grad(loss, [planes, pal, cam, focal])
+        return loss, rgb, depth, mask, grads
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    # ---- `value`: inputs resident in HBM ------------------------------------------------------
+    leaves = [t.to(dev).requires_grad_() for t in (planes_h, pal_h, cam_h, focal_h)]
+    target = target_h.to(dev)
+    torch.manual_seed(1234 + rank)
+    for _ in range(args.warmup):
+        step(*leaves, target)
+    barrier()
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+        time.sleep(0.3)
+    timed = ("nfi_field_fwd", "nfi_field_bwd")
+    _lib.PROFILE.start(timed)
+    barrier()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(args.steps):
+        step(*leaves, target)
+    e1.record()
+    barrier()
+    _lib.PROFILE.stop()
+    ms_total = e0.elapsed_time(e1)
+    launches = _lib.PROFILE.launches
+    durs = _lib.PROFILE.durations_ms()
+    clocks = sampler.finish() if rank == 0 else None
+
+    # ---- `e2e`: host buffers in, host buffers out, through the public API ---------------------
+    pin = lambda t: t.contiguous().pin_memory()
+    host_in = [pin(t) for t in (planes_h, pal_h, cam_h, focal_h, target_h)]
+    host_out = [pin(torch.empty(s)) for s in ((), (B, H, W, 3), (B, H, W), (B, H, W), tuple(planes_h.shape),
+                                              tuple(pal_h.shape), (B, 4, 4), (B,))]
+    h2d = sum(t.numel() * 4 for t in host_in)
+    d2h = sum(t.numel() * 4 for t in host_out)
+
+    def e2e_step():
+        p, a, c, f, tg = [t.to(dev, non_blocking=True) for t in host_in]
+        loss, rgb, depth, mask, g = step(p.requires_grad_(), a.requires_grad_(), c.requires_grad_(),
+                                         f.requires_grad_(), tg)
+        for dst, src in zip(host_out, (loss, rgb, depth, mask, *g)):
+            dst.copy_(src.detach(), non_blocking=True)
+        torch.cuda.current_stream().synchronize()       # the caller reads the host results
+        return float(host_out[0])
+
+    for _ in range(max(1, min(args.warmup, 3))):
+        e2e_step()
+    barrier()
+    n_e2e = max(3, min(args.steps, 10))
+    t0 = time.perf_counter()
+    f0, f1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    f0.record()
+    for _ in range(n_e2e):
+        e2e_step()
+    f1.record()
+    barrier()
+    e2e_ms = f0.elapsed_time(f1)
+    del t0
+
+    # max over ranks
+    if world > 1:
+        t = torch.tensor([ms_total, e2e_ms], device=dev, dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms_total, e2e_ms = float(t[0]), float(t[1])
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+    ms_step = ms_total / args.steps
+    value = world * R / (ms_step * 1e-3)
+    e2e_value = world * R / (e2e_ms / n_e2e * 1e-3)
+    pk, pk_src = peaks()
+    # dominant kernel: field_bwd_kernel (one launch = one 64-sample pass over every ray)
+    samples = R * S
+    bwd = durs.get("nfi_field_bwd", [])
+    fwd = durs.get("nfi_field_fwd", [])
+    bwd_ms = sum(bwd) / max(1, len(bwd))
+    fwd_ms = sum(fwd) / max(1, len(fwd))
+    # algorithmic bytes of ONE field_bwd launch (DESIGN.md "field_bwd"): planes read once + plane
+    # gradient written once + per sample (upstream float4 16 + depth 4 + d/d point 12) + rays 24 B
+    a_bytes = 2 * B * PLANE_BYTES + samples * (16 + 4 + 12) + R * 24
+    ach = a_bytes / (bwd_ms * 1e-3) / 1e9 if bwd_ms > 0 else None
+    mlp_flops_bwd = samples * 5504              # backward-data only; the recompute is overhead
+    out = {
+        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": "config2: inversion render fwd+bwd, B=%d images/GPU, %dx%d rays, 64+64 samples/ray, "
+                               "perspective, grads to planes/attention/cam/focal" % (B, H, W),
+                   "rays_per_step_per_gpu": R, "l2": "inputs (planes %d MB + gradients) exceed the 126 MB L2; no flush"
+                   % (B * PLANE_BYTES >> 20), "rng": "torch.rand uniforms drawn per step (parity mode)"},
+        "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+                "steps": n_e2e, "ms_per_step": e2e_ms / n_e2e},
+        "gpu_launches": launches,
+        "clocks": clocks,
+        "roofline": {"bound": "hbm", "kernel": "field_bwd_kernel", "achieved": ach, "peak": pk["hbm_gbs"],
+                     "unit": "GB/s", "frac": (ach / pk["hbm_gbs"]) if ach else None, "traffic": None,
+                     "peak_source": pk_src, "algorithmic_bytes_per_launch": a_bytes,
+                     "launch_ms": bwd_ms, "launches_timed": len(bwd),
+                     "share_of_step": (sum(bwd) / args.steps) / ms_step if ms_step else None,
+                     "mlp_tflops_bwd_data": mlp_flops_bwd / (bwd_ms * 1e-3) / 1e12 if bwd_ms > 0 else None,
+                     "field_fwd_launch_ms": fwd_ms,
+                     "field_fwd_share_of_step": (sum(fwd) / args.steps) / ms_step if ms_step else None},
+    }
+    if not args.no_cpu_baseline and world == 1:
+        out["cpu_baseline"] = cpu_baseline(sample_res=args.cpu_res)
+    elif world > 1:
+        out["cpu_baseline"] = None
+    print(json.dumps(out))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+# ---------------------------------------------------------------------------------------------
+# CPU arm: the oracle port of the reference's PyTorch path (the reference itself is Python and
+# cannot travel to the GPU box; oracle/nfi_oracle.py is pinned to it by tests/golden/*).
+# ---------------------------------------------------------------------------------------------
+def cpu_step_fn(B, res):
+    import nfi_oracle as O
+    H = W = res
+    S = 64
+    planes, fd, pal, cam, focal, target = make_inputs(B, H, W, S)
+    fp = O.FieldParams(fd["W0"], fd["b0"], fd["W1"], fd["b1"], SCENE_RANGE, True, 10, fd["beta"], fd["alpha"])
+    g = torch.Generator().manual_seed(1234)
+
+    def step():
+        p = planes.clone().requires_grad_()
+        a = pal.clone().requires_grad_()
+        c = cam.clone().requires_grad_()
+        f = focal.clone().requires_grad_()
+        u_s = torch.rand(B, H, W, S, generator=g)
+        u_p = torch.rand(B * H * W, S, generator=g)
+        rgb, depth, mask = O.render(p.view(B, 3, 32, 256, 256), a, fp, H, W, c, f, None, None, S, False, u_s, u_p)
+        loss = (rgb - target).abs().mean() * B
+        torch.autograd.grad(loss, [p, a, c, f])
+        return float(loss)
+
+    return step, B * H * W
+
+
+def cpu_baseline(sample_res=64):
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    step, rays = cpu_step_fn(1, sample_res)
+    step()                                   # warm-up
+    n, t0 = 0, time.perf_counter()
+    while True:
+        step()
+        n += 1
+        dt = time.perf_counter() - t0
+        if dt > 12.0 or n >= 8:
+            break
+    return {"value": rays * n / dt, "unit": UNIT, "cores": cores, "kind": "port",
+            "sample": "oracle port of the reference PyTorch path, 1 image %dx%d rays (64+64 samples), fwd+bwd, "
+                      "%d timed steps after 1 warm-up, torch CPU with %d threads" % (sample_res, sample_res, n, cores)}
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    res = args.cpu_res
+    step, rays = cpu_step_fn(1, res)
+    for _ in range(args.warmup):
+        step()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        step()
+    dt = time.perf_counter() - t0
+    value = rays * args.steps / dt
+    sample = ("each step = bounded sample of config 2: 1 image %dx%d rays (64+64 samples/ray), fwd+bwd, oracle "
+              "port of the reference PyTorch CPU path, %d torch threads" % (res, res, cores))
+    print(json.dumps({
+        "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": int(os.environ.get("WORLD_SIZE", "1")),
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": "config2: inversion render fwd+bwd (CPU arm: " + sample + ")"},
+        "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
+        "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+    }))
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--batch", type=int, default=16, help="images per GPU (config 2: 16)")
+    ap.add_argument("--res", type=int, default=128)
+    ap.add_argument("--cpu-res", type=int, default=64, help="image size of the bounded CPU sample")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl == "ours" else max(args.warmup, 1)
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_ours(args)
+
+
+if __name__ == "__main__":
+    main()

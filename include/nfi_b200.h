@@ -129,6 +129,10 @@ int nfi_sample_pdf(const float* bins, const float* weights, int64_t R, int M, in
 int nfi_importance(const float* sigma, int sigma_stride, const float* dirs, const float* z_coarse,
                    int64_t R, int S, const float* u, float* z_fine, nfi_stream_t stream);
 
+/* ---- nerf_utils.cumprod_exclusive (lib/nerf_utils.py:20-25): x [R,n] -> out [R,n], forward only
+ *      (the reference only uses it inside render_volume_density*, which have their own kernels). */
+int nfi_cumprod_exclusive(const float* x, int64_t R, int n, float* out, nfi_stream_t stream);
+
 /* ---- A10: nerf_utils.render_volume_density (lib/nerf_utils.py:125-163) -------------------------
  * sigma [R,S], rgb [R,S,3], z [R,S], dirs [R,3]; optional normals [R,S,3], semantics [R,S,n_sem]. */
 int nfi_composite_fwd(const float* sigma, const float* rgb, const float* dirs, const float* z,

@@ -329,7 +329,47 @@ merge_composite_bwd_kernel(const float4* __restrict__ coarse, const float4* __re
   }
 }
 
+// ------------------------------------------------------------------------------------------
+// cumprod_exclusive (lib/nerf_utils.py:20-25): out[i] = prod_{j<i} x[j], out[0] = 1.  One warp per
+// row, 128 elements per pass with a carried fp64 running product (ATen's CPU accumulator type).
+// ------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(kThreads)
+cumprod_exclusive_kernel(const float* __restrict__ x, int64_t R, int n, float* __restrict__ out) {
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int64_t nwarps = (int64_t)gridDim.x * kWarps;
+  for (int64_t r = (int64_t)blockIdx.x * kWarps + warp; r < R; r += nwarps) {
+    double carry = 1.0;
+    for (int base = 0; base < n; base += 32 * E) {
+      float v[E];
+      double pre[E];
+      double local = 1.0;
+#pragma unroll
+      for (int e = 0; e < E; ++e) {
+        const int i = base + lane * E + e;
+        v[e] = i < n ? x[r * n + i] : 1.f;
+        pre[e] = local;
+        local = NFI_DMUL(local, (double)v[e]);
+      }
+      const double below = NFI_DMUL(carry, nfi_warp_exclusive_prod(local, lane));
+#pragma unroll
+      for (int e = 0; e < E; ++e) {
+        const int i = base + lane * E + e;
+        if (i < n) out[r * n + i] = (float)NFI_DMUL(below, pre[e]);
+      }
+      carry = __shfl_sync(NFI_FULL, NFI_DMUL(below, local), 31);
+    }
+  }
+}
+
 }  // namespace
+
+extern "C" int nfi_cumprod_exclusive(const float* x, int64_t R, int n, float* out, nfi_stream_t stream) {
+  NFI_REQUIRE(x && out, NFI_ERR_BAD_ARG, "nfi_cumprod_exclusive: NULL pointer");
+  NFI_REQUIRE(R > 0 && n > 0, NFI_ERR_BAD_ARG, "nfi_cumprod_exclusive: bad sizes");
+  cumprod_exclusive_kernel<<<warp_grid(R), kThreads, 0, nfi_cu(stream)>>>(x, R, n, out);
+  NFI_CHECK_LAUNCH("cumprod_exclusive_kernel");
+  return NFI_OK;
+}
 
 extern "C" int nfi_composite_fwd(const float* sigma, const float* rgb, const float* dirs, const float* z,
                                  const float* normals, const float* semantics, int n_sem, int64_t R,

@@ -1,0 +1,424 @@
+"""torch.autograd.Function wrappers, one per kernel group of libnfi_b200.so.
+
+Each forward/backward is one (or a few) C-ABI calls on the caller's current CUDA stream; every
+buffer -- outputs, workspaces, saved-for-backward state -- is a torch tensor, so the caching
+allocator and autograd own all lifetimes ("Ownership").  Backward is
+once-differentiable.  Nothing here computes on the CPU or falls back to PyTorch ops.
+"""
+from __future__ import annotations
+
+import torch
+from torch.autograd import Function
+from torch.autograd.function import once_differentiable
+
+from . import _lib
+from ._lib import call, f32c, ptr
+
+NEARFAR_WS_BYTES = 16384
+
+
+def _empty(ref, *shape, dtype=torch.float32):
+    return torch.empty(shape, dtype=dtype, device=ref.device)
+
+
+# ---------------------------------------------------------------------------------------------
+# A1  rays     lib/nerf_utils.py:28-93 (+ F.normalize, run.py:196)
+# ---------------------------------------------------------------------------------------------
+class _RayBundle(Function):
+    @staticmethod
+    def forward(ctx, cam2world, focal, center, bbox, H, W, normalize):
+        cam = f32c(cam2world)
+        B = cam.shape[0]
+        fo = None if focal is None else f32c(focal.reshape(-1))
+        fstride = 0
+        if fo is not None:
+            assert fo.numel() in (1, B), "focal_length must be 0-dim, [1] or [B]"
+            fstride = 1 if (fo.numel() == B and focal.dim() > 0) else 0
+        ce = f32c(center)
+        bb = f32c(bbox)
+        o = _empty(cam, B, H, W, 3)
+        d = _empty(cam, B, H, W, 3)
+        call("nfi_ray_bundle_fwd", cam, ptr(cam), ptr(fo), fstride, ptr(ce), ptr(bb), B, H, W,
+             int(normalize), ptr(o), ptr(d))
+        ctx.save_for_backward(cam, fo, ce, bb)
+        ctx.meta = (B, H, W, int(normalize), fstride, None if focal is None else focal.shape)
+        return o, d
+
+    @staticmethod
+    @once_differentiable
+    def backward(ctx, go, gd):
+        cam, fo, ce, bb = ctx.saved_tensors
+        B, H, W, normalize, fstride, fshape = ctx.meta
+        go = f32c(go)
+        gd = f32c(gd)
+        g_cam = _empty(cam, B, 4, 4)
+        g_focal = _empty(cam, B)
+        call("nfi_ray_bundle_bwd", cam, ptr(cam), ptr(fo), fstride, ptr(ce), ptr(bb), B, H, W, normalize,
+             ptr(go), ptr(gd), ptr(g_cam), ptr(g_focal))
+        gf = None
+        if fo is not None and ctx.needs_input_grad[1]:
+            gf = (g_focal if fstride == 1 else g_focal.sum()).reshape(fshape)
+        return g_cam, gf, None, None, None, None, None
+
+
+def ray_bundle(H, W, focal, cam2world, bbox=None, center=None, normalize=False):
+    return _RayBundle.apply(cam2world, focal, center, bbox, int(H), int(W), bool(normalize))
+
+
+# ---------------------------------------------------------------------------------------------
+# A2  near / far   lib/nerf_utils.py:227-275 (always under no_grad in the reference, run.py:197)
+# ---------------------------------------------------------------------------------------------
+def near_far(origins, dirs, scene_range, check_hits=True):
+    o = f32c(origins.detach())
+    d = f32c(dirs.detach())
+    shape = o.shape[:-1]
+    R = o.numel() // 3
+    near = _empty(o, *shape)
+    far = _empty(o, *shape)
+    ws = _empty(o, NEARFAR_WS_BYTES, dtype=torch.uint8)
+    call("nfi_near_far", o, ptr(o), ptr(d), R, float(scene_range), ptr(near), ptr(far), ptr(ws))
+    if check_hits:
+        hits = int(ws[:4].view(torch.int32).item())
+        if hits == 0:
+            # the reference raises from near_plane[mask].min() on an empty tensor (nerf_utils.py:260)
+            raise RuntimeError("compute_near_far_planes: no ray intersects the scene box "
+                               "(min(): expected a non-empty tensor)")
+    return near, far
+
+
+# ---------------------------------------------------------------------------------------------
+# A3  stratified depths + query points   lib/nerf_utils.py:96-122
+# ---------------------------------------------------------------------------------------------
+def stratified(near, far, S, randomize, u=None, seed=0, offset=0):
+    n = f32c(near)
+    f = f32c(far)
+    R = n.numel()
+    z = _empty(n, *n.shape, S)
+    uu = f32c(u)
+    if uu is not None:
+        assert uu.numel() == R * S
+    call("nfi_stratified", n, ptr(n), ptr(f), ptr(uu), R, int(S), int(bool(randomize)), int(seed),
+         int(offset), ptr(z))
+    return z
+
+
+class _Points(Function):
+    @staticmethod
+    def forward(ctx, origins, dirs, z):
+        o, d, zz = f32c(origins), f32c(dirs), f32c(z)
+        S = zz.shape[-1]
+        R = zz.numel() // S
+        pts = _empty(o, *zz.shape, 3)
+        call("nfi_points_fwd", o, ptr(o), ptr(d), ptr(zz), R, S, ptr(pts))
+        ctx.save_for_backward(zz)
+        ctx.oshape = o.shape
+        return pts
+
+    @staticmethod
+    @once_differentiable
+    def backward(ctx, g):
+        (zz,) = ctx.saved_tensors
+        g = f32c(g)
+        S = zz.shape[-1]
+        R = zz.numel() // S
+        go = _empty(zz, *ctx.oshape)
+        gd = _empty(zz, *ctx.oshape)
+        call("nfi_points_bwd", zz, ptr(g), ptr(zz), R, S, ptr(go), ptr(gd))
+        return go, gd, None
+
+
+def points_on_rays(origins, dirs, z):
+    return _Points.apply(origins, dirs, z.detach())
+
+
+# ---------------------------------------------------------------------------------------------
+# layout boundary: [B, 96, Hp, Wp] NCHW (models/generator.py:475-477) <-> [B, 3, Hp, Wp, 32]
+# ---------------------------------------------------------------------------------------------
+class _PlanesToCL(Function):
+    @staticmethod
+    def forward(ctx, planes):
+        p = f32c(planes)
+        B, Hp, Wp = p.shape[0], p.shape[-2], p.shape[-1]
+        assert p.numel() == B * 96 * Hp * Wp, "planes must be [B, 96, Hp, Wp] or [B, 3, 32, Hp, Wp]"
+        out = _empty(p, B, 3, Hp, Wp, 32)
+        call("nfi_planes_to_cl", p, ptr(p), B, Hp, Wp, ptr(out))
+        ctx.shape = planes.shape
+        return out
+
+    @staticmethod
+    @once_differentiable
+    def backward(ctx, g):
+        g = f32c(g)
+        B, _, Hp, Wp, _ = g.shape
+        out = _empty(g, *ctx.shape)
+        call("nfi_planes_grad_from_cl", g, ptr(g), B, Hp, Wp, ptr(out))
+        return out
+
+
+def planes_to_channels_last(planes):
+    return _PlanesToCL.apply(planes)
+
+
+# ---------------------------------------------------------------------------------------------
+# A4-A6  triplane gather + decoder MLP + density/colour heads, fused
+#        models/generator.py:288-331, 587-681; models/stylegan.py:148-180
+# ---------------------------------------------------------------------------------------------
+class FieldConfig:
+    """Static description of the decoder heads (mirrors NfiField's scalar members)."""
+
+    def __init__(self, attention_values=10, use_sdf=True, scene_range=1.0):
+        self.attention_values = int(attention_values)
+        self.use_sdf = bool(use_sdf)
+        self.scene_range = float(scene_range)
+
+
+def _param_sizes(n_out):
+    return [64 * 32, 64, n_out * 64, n_out, 1, 1]
+
+
+class _Field(Function):
+    """inputs: planes_cl [B,3,Hp,Wp,32], palette [B,A,3]|None, W0,b0,W1,b1,beta,alpha,
+    then EITHER (origins, dirs [B*npi,3], z [B*npi,S]) OR points [B,n,3].
+    mode 0 -> out[..., 4] = (sigma, r, g, b); mode 1 -> raw decoder output [..., n_out]."""
+
+    @staticmethod
+    def forward(ctx, planes_cl, palette, W0, b0, W1, b1, beta, alpha, origins, dirs, z, points,
+                cfg, mode, img_w, skip_oob, want_probs):
+        pl = f32c(planes_cl)
+        B, _, Hp, Wp, C = pl.shape
+        assert C == 32 and pl.shape[1] == 3
+        pal = f32c(palette)
+        field, keep = _lib.make_field_struct(W0, b0, W1, b1, beta, alpha, cfg.attention_values,
+                                             cfg.use_sdf, cfg.scene_range)
+        n_out = field.n_out
+        if points is not None:
+            pts = f32c(points)
+            npi = pts.numel() // 3 // B
+            S = 1
+            o = d = zz = None
+            lead = pts.shape[:-1]
+        else:
+            o, d, zz = f32c(origins), f32c(dirs), f32c(z)
+            S = zz.shape[-1]
+            npi = zz.numel() // S // B
+            pts = None
+            lead = zz.shape
+        width = 4 if mode == 0 else n_out
+        out = _empty(pl, *lead, width)
+        probs = None
+        if want_probs and mode == 0 and cfg.attention_values > 0:
+            probs = _empty(pl, *lead, cfg.attention_values)
+        call("nfi_field_fwd", pl, field, ptr(pl), ptr(pal), B, Hp, Wp, ptr(o), ptr(d), ptr(zz), ptr(pts),
+             npi, S, mode, int(img_w), int(skip_oob), ptr(out), ptr(probs))
+        ctx.save_for_backward(pl, pal, *keep[:4], keep[4], keep[5], o, d, zz, pts)
+        ctx.cfg, ctx.mode, ctx.img_w, ctx.npi, ctx.S = cfg, mode, int(img_w), npi, S
+        ctx.oshape = None if origins is None else origins.shape
+        ctx.pshape = None if points is None else points.shape
+        if probs is not None:
+            ctx.mark_non_differentiable(probs)
+            return out, probs
+        return out, None
+
+    @staticmethod
+    @once_differentiable
+    def backward(ctx, g_out, _g_probs):
+        pl, pal, W0, b0, W1, b1, beta, alpha, o, d, zz, pts = ctx.saved_tensors
+        cfg, mode = ctx.cfg, ctx.mode
+        need = ctx.needs_input_grad
+        if any(need[2:6]):
+            raise NotImplementedError("nfi_b200: decoder weight gradients (W0, b0, W1, b1) are not "
+                                      "produced by the fused backward yet")
+        B, _, Hp, Wp, _ = pl.shape
+        field, keep = _lib.make_field_struct(W0, b0, W1, b1, beta, alpha, cfg.attention_values,
+                                             cfg.use_sdf, cfg.scene_range)
+        n_out = field.n_out
+        g = f32c(g_out)
+        g_planes = torch.zeros_like(pl) if need[0] else None
+        g_pal = torch.zeros_like(pal) if (pal is not None and need[1] and mode == 0) else None
+        want_pts = (need[8] or need[9]) if pts is None else need[11]
+        g_points = _empty(pl, *g.shape[:-1], 3) if want_pts else None
+        want_params = cfg.use_sdf and mode == 0 and (need[6] or need[7])
+        g_params = torch.zeros(sum(_param_sizes(n_out)), dtype=torch.float32, device=pl.device) \
+            if want_params else None
+        call("nfi_field_bwd", pl, field, ptr(pl), ptr(pal), B, Hp, Wp, ptr(o), ptr(d), ptr(zz), ptr(pts),
+             ctx.npi, ctx.S, mode, ctx.img_w, ptr(g), ptr(g_planes), ptr(g_pal), ptr(g_points),
+             ptr(g_params))
+        go = gd = gp = None
+        if want_pts:
+            if pts is None:
+                R = zz.numel() // ctx.S
+                go = _empty(pl, *ctx.oshape)
+                gd = _empty(pl, *ctx.oshape)
+                call("nfi_points_bwd", pl, ptr(g_points), ptr(zz), R, ctx.S, ptr(go), ptr(gd))
+            else:
+                gp = g_points.view(ctx.pshape)
+        g_beta = g_alpha = None
+        if g_params is not None:
+            base = sum(_param_sizes(n_out)[:4])
+            g_beta = g_params[base:base + 1].view_as(beta) if need[6] else None
+            g_alpha = g_params[base + 1:base + 2].view_as(alpha) if need[7] else None
+        return (g_planes, g_pal, None, None, None, None, g_beta, g_alpha, go, gd, None, gp,
+                None, None, None, None, None)
+
+
+def field_on_rays(planes_cl, palette, W0, b0, W1, b1, beta, alpha, origins, dirs, z, cfg,
+                  img_w=0, skip_oob=False, want_probs=False):
+    """(sigma, r, g, b) [.., S, 4] for the samples o + d*z of every ray (no points tensor in HBM)."""
+    return _Field.apply(planes_cl, palette, W0, b0, W1, b1, beta, alpha, origins, dirs, z.detach(),
+                        None, cfg, 0, img_w, skip_oob, want_probs)
+
+
+def field_on_points(planes_cl, palette, W0, b0, W1, b1, beta, alpha, points, cfg, mode=0,
+                    want_probs=False):
+    """Heads (mode 0) or raw decoder output (mode 1) at explicit points [B, n, 3]."""
+    return _Field.apply(planes_cl, palette, W0, b0, W1, b1, beta, alpha, None, None, None, points,
+                        cfg, mode, 0, False, want_probs)
+
+
+# ---------------------------------------------------------------------------------------------
+# A7 / A8  coarse weights, EG3D smoothing, inverse-CDF sampling (all under no_grad in the
+#          reference: run.py:261-281)
+# ---------------------------------------------------------------------------------------------
+def weights_only(sigma, dirs, z, smooth=False, sigma_stride=1):
+    """sigma [.., S] (or a strided view base with `sigma_stride` floats between samples)."""
+    zz = f32c(z.detach())
+    S = zz.shape[-1]
+    R = zz.numel() // S
+    sg = f32c(sigma.detach())
+    d = f32c(dirs.detach())
+    w = _empty(zz, *zz.shape)
+    call("nfi_weights_only", zz, ptr(sg), int(sigma_stride), ptr(d), ptr(zz), R, S, int(smooth), ptr(w))
+    return w
+
+
+def sample_pdf(bins, weights, n, u=None, return_indices=False):
+    b = f32c(bins.detach())
+    w = f32c(weights.detach())
+    R, M = b.shape
+    assert w.shape == (R, M - 1)
+    uu = f32c(u)
+    out = _empty(b, R, n)
+    inds = _empty(b, R, n, dtype=torch.int32) if return_indices else None
+    call("nfi_sample_pdf", b, ptr(b), ptr(w), R, M, int(n), ptr(uu), ptr(out), ptr(inds))
+    return (out, inds) if return_indices else out
+
+
+def importance(sigma, dirs, z_coarse, u=None, sigma_stride=1):
+    """run.py:261-281 in one kernel: coarse sigma + depths -> S fine depths per ray."""
+    zc = f32c(z_coarse.detach())
+    S = zc.shape[-1]
+    R = zc.numel() // S
+    sg = f32c(sigma.detach())
+    d = f32c(dirs.detach())
+    uu = f32c(u)
+    zf = _empty(zc, *zc.shape)
+    call("nfi_importance", zc, ptr(sg), int(sigma_stride), ptr(d), ptr(zc), R, S, ptr(uu), ptr(zf))
+    return zf
+
+
+def cumprod_exclusive(x):
+    """lib/nerf_utils.py:20-25 (forward only)."""
+    xx = f32c(x.detach())
+    n = xx.shape[-1]
+    out = torch.empty_like(xx)
+    call("nfi_cumprod_exclusive", xx, ptr(xx), xx.numel() // n, n, ptr(out))
+    return out
+
+
+# ---------------------------------------------------------------------------------------------
+# A10  alpha compositing   lib/nerf_utils.py:125-163
+# ---------------------------------------------------------------------------------------------
+class _Composite(Function):
+    @staticmethod
+    def forward(ctx, sigma, rgb, dirs, z, normals, semantics, white):
+        sg, col, d, zz = f32c(sigma), f32c(rgb), f32c(dirs), f32c(z)
+        nrm, sem = f32c(normals), f32c(semantics)
+        S = zz.shape[-1]
+        R = zz.numel() // S
+        lead = zz.shape[:-1]
+        n_sem = 0 if sem is None else sem.shape[-1]
+        rgb_map = _empty(zz, *lead, 3)
+        depth = _empty(zz, *lead)
+        mask = _empty(zz, *lead)
+        nmap = _empty(zz, *lead, 3) if nrm is not None else None
+        smap = _empty(zz, *lead, n_sem) if sem is not None else None
+        call("nfi_composite_fwd", zz, ptr(sg), ptr(col), ptr(d), ptr(zz), ptr(nrm), ptr(sem), n_sem, R, S,
+             int(white), ptr(rgb_map), ptr(depth), ptr(mask), ptr(nmap), ptr(smap))
+        ctx.save_for_backward(sg, col, d, zz, sem)
+        ctx.white = int(white)
+        ctx.mark_non_differentiable(depth)
+        if nmap is not None:
+            ctx.mark_non_differentiable(nmap)   # gradient to `normals` is not produced (N1, next)
+        return rgb_map, depth, mask, nmap, smap
+
+    @staticmethod
+    @once_differentiable
+    def backward(ctx, g_rgb_map, _g_depth, g_mask, _g_nmap, g_smap):
+        sg, col, d, zz, sem = ctx.saved_tensors
+        S = zz.shape[-1]
+        R = zz.numel() // S
+        n_sem = 0 if sem is None else sem.shape[-1]
+        g_rgb_map = f32c(g_rgb_map)
+        g_mask = f32c(g_mask)
+        g_smap = f32c(g_smap) if sem is not None else None
+        if g_rgb_map is None:
+            g_rgb_map = torch.zeros(*zz.shape[:-1], 3, dtype=torch.float32, device=zz.device)
+        g_sigma = _empty(zz, *zz.shape)
+        g_rgb = _empty(zz, *col.shape) if ctx.needs_input_grad[1] else None
+        g_dirs = _empty(zz, *d.shape) if ctx.needs_input_grad[2] else None
+        g_sem = torch.zeros_like(sem) if (sem is not None and ctx.needs_input_grad[5]) else None
+        call("nfi_composite_bwd", zz, ptr(sg), ptr(col), ptr(d), ptr(zz), ptr(sem), n_sem, R, S, ctx.white,
+             ptr(g_rgb_map), ptr(g_mask), ptr(g_smap), ptr(g_sigma), ptr(g_rgb), ptr(g_dirs), ptr(g_sem))
+        return g_sigma, g_rgb, g_dirs, None, None, g_sem, None
+
+
+def composite(sigma, rgb, dirs, z, normals=None, semantics=None, white_background=True):
+    return _Composite.apply(sigma, rgb, dirs, z.detach(), normals, semantics, bool(white_background))
+
+
+# ---------------------------------------------------------------------------------------------
+# A9 + A10 fused: depth merge of coarse + fine samples and compositing   run.py:283-348
+# ---------------------------------------------------------------------------------------------
+class _MergeComposite(Function):
+    @staticmethod
+    def forward(ctx, coarse, fine, z_coarse, z_fine, dirs, white, cam2world):
+        c, f = f32c(coarse), f32c(fine)
+        zc, zf, d = f32c(z_coarse), f32c(z_fine), f32c(dirs)
+        S = zc.shape[-1]
+        R = zc.numel() // S
+        lead = zc.shape[:-1]
+        cam = f32c(cam2world)
+        rpi = R // cam.shape[0] if cam is not None else 0
+        rgb_map = _empty(zc, *lead, 3)
+        depth = _empty(zc, *lead)
+        mask = _empty(zc, *lead)
+        perm = _empty(zc, *lead, 2 * S, dtype=torch.uint8)
+        zs = _empty(zc, *lead, 2 * S)
+        call("nfi_merge_composite_fwd", zc, ptr(c), ptr(f), ptr(zc), ptr(zf), ptr(d), R, S, int(white),
+             ptr(cam), rpi, ptr(rgb_map), ptr(depth), ptr(mask), ptr(perm), ptr(zs))
+        ctx.save_for_backward(c, f, zs, perm, d)
+        ctx.white = int(white)
+        ctx.mark_non_differentiable(depth, perm, zs)
+        return rgb_map, depth, mask, perm, zs
+
+    @staticmethod
+    @once_differentiable
+    def backward(ctx, g_rgb_map, _gd, g_mask, _gp, _gz):
+        c, f, zs, perm, d = ctx.saved_tensors
+        S = c.shape[-2]
+        R = c.numel() // (4 * S)
+        g_rgb_map = f32c(g_rgb_map)
+        g_mask = f32c(g_mask)
+        g_c = torch.empty_like(c)
+        g_f = torch.empty_like(f)
+        call("nfi_merge_composite_bwd", c, ptr(c), ptr(f), ptr(zs), ptr(perm), ptr(d), R, S, ctx.white,
+             ptr(g_rgb_map), ptr(g_mask), ptr(g_c), ptr(g_f))
+        # d|dir| is not returned: render() passes unit directions, whose norm has a zero
+        # gradient after F.normalize's projection (run.py:196).
+        return g_c, g_f, None, None, None, None, None
+
+
+def merge_composite(coarse, fine, z_coarse, z_fine, dirs, white_background, cam2world_for_zbuffer=None):
+    """coarse / fine: (sigma, r, g, b) [.., S, 4].  Returns rgb, depth, mask, perm (uint8), z_sorted."""
+    return _MergeComposite.apply(coarse, fine, z_coarse.detach(), z_fine.detach(), dirs.detach(),
+                                 bool(white_background), cam2world_for_zbuffer)

@@ -1,0 +1,109 @@
+"""The fused render: `run.py::render` (run.py:176-350; the six script-local copies, the z-buffer
+variant at eval_kitti_persp.py:221-228) rebuilt ray-major on the sm_100a kernels.
+
+Two entry points:
+  * `render_planes(...)`  -- the hot path proper, on explicit tensors (planes, attention values,
+    decoder weights, camera).  Query points, gathered features, hidden activations and per-sample
+    sort indices never reach HBM; what does: rays, depths, one float4 per sample, the images.
+  * `make_render(args, dataset_config)` -> `render(target_model, height, width, ...)` with the
+    reference's exact signature and 6-tuple return, for `ParallelModel.forward` (run.py:597-611).
+"""
+from __future__ import annotations
+
+from typing import Optional
+
+import torch
+
+from . import ops
+from .decoder import Field, _as_planes_tensor
+
+
+def render_planes(planes, palette, field: Field, height: int, width: int, tform_cam2world,
+                  focal_length=None, center=None, bbox=None, depth_samples_per_ray: int = 64,
+                  randomize: bool = True, white_background: bool = False, fine_sampling: bool = True,
+                  force_no_cam_grad: bool = False, zbuffer_depth: bool = False,
+                  planes_layout: str = "nchw", u_strat=None, u_pdf=None, check_hits: bool = True,
+                  return_aux: bool = False):
+    """Render `B` images.  planes: [B,96,Hp,Wp] or [B,3,32,Hp,Wp] (layout 'nchw', the StyleGAN2
+    output of models/generator.py:475-477) or [B,3,Hp,Wp,32] ('cl').  palette: attention values
+    [B,A,3] (None for the plain RGB head).  Returns (rgb [B,H,W,3], depth [B,H,W], mask [B,H,W])
+    (+ aux dict).  `u_strat` [B,H,W,S] / `u_pdf` [B*H*W,S] override the uniforms that are
+    otherwise drawn with torch.rand in the reference's order (nerf_utils.py:115, :204)."""
+    H, W, S = int(height), int(width), int(depth_samples_per_ray)
+    cam = tform_cam2world
+    B = cam.shape[0]
+    dev = cam.device
+    # A1 (+ F.normalize, run.py:196), A2 (no_grad, run.py:197-200), A3 depths
+    o, d = ops.ray_bundle(H, W, focal_length, cam, bbox, center, normalize=True)
+    near, far = ops.near_far(o, d, field.cfg.scene_range, check_hits=check_hits)
+    if randomize and u_strat is None:
+        u_strat = torch.rand((B, H, W, S), dtype=torch.float32, device=dev)
+    z_c = ops.stratified(near, far, S, randomize, u_strat if randomize else None)
+    if force_no_cam_grad:                       # run.py:211-214
+        o_s, d_s = o.detach(), d.detach()
+    else:
+        o_s, d_s = o, d
+    planes_cl = planes if planes_layout == "cl" else ops.planes_to_channels_last(planes)
+    wts = field.tensors()
+    # A4-A6 on the coarse samples: (sigma, r, g, b) per sample
+    coarse, _ = ops.field_on_rays(planes_cl, palette, *wts, o_s, d_s, z_c, field.cfg, img_w=W,
+                                  skip_oob=True)
+    aux = {"origins": o, "dirs": d, "near": near, "far": far, "z_coarse": z_c}
+    if fine_sampling:
+        # A7 + A8 (no_grad, run.py:261-281)
+        if randomize and u_pdf is None:
+            u_pdf = torch.rand((B * H * W, S), dtype=torch.float32, device=dev)
+        z_f = ops.importance(coarse, d, z_c, u_pdf if randomize else None, sigma_stride=4)
+        fine, _ = ops.field_on_rays(planes_cl, palette, *wts, o_s, d_s, z_f, field.cfg, img_w=W,
+                                    skip_oob=True)
+        # A9 + A10
+        rgb, depth, mask, perm, z_sorted = ops.merge_composite(
+            coarse, fine, z_c, z_f, d, white_background, cam.detach() if zbuffer_depth else None)
+        aux.update(z_fine=z_f, perm=perm, z_sorted=z_sorted)
+    else:
+        rgb, depth, mask, _, _ = ops.composite(coarse[..., 0], coarse[..., 1:], d.detach(), z_c,
+                                               None, None, white_background)
+        if zbuffer_depth:
+            raise NotImplementedError("z-buffer depth without fine sampling")
+    if return_aux:
+        return rgb, depth, mask, aux
+    return rgb, depth, mask
+
+
+def _closure_vars(fn):
+    return dict(zip(fn.__code__.co_freevars, (c.cell_contents for c in fn.__closure__ or ())))
+
+
+def make_render(args, dataset_config, zbuffer_depth: bool = False):
+    """Build a `render` with the reference's signature (run.py:176-191), bound to the script's
+    `args` (use_viewdir, use_sdf, attention_values, fine_sampling) and `dataset_config`
+    (scene_range, white_background) globals that the reference function reads (run.py:200-348)."""
+
+    def render(target_model, height, width, tform_cam2world, focal_length, center, bbox, model_input,
+               depth_samples_per_ray, randomize=True, compute_normals=False, compute_semantics=False,
+               compute_coords=False, extra_model_outputs=[], extra_model_inputs={},
+               force_no_cam_grad=False):
+        if args.use_viewdir:
+            raise NotImplementedError("nfi_b200.render: use_viewdir is not covered (SURVEY.md 8(f) N4)")
+        if compute_normals or compute_semantics or compute_coords:
+            raise NotImplementedError("nfi_b200.render: normals / semantics / coords outputs are not "
+                                      "covered yet (SURVEY.md 8(f) N1)")
+        # The generator still produces planes and attention values (StyleGAN2 synthesis, out of
+        # scope); the closure it returns holds them -- read them instead of calling it.
+        model_outputs = target_model(None, model_input, ["sampler"] + list(extra_model_outputs),
+                                     extra_model_inputs)
+        sampler = model_outputs.pop("sampler")
+        cv = _closure_vars(sampler)
+        gen = cv["self"]
+        planes = _as_planes_tensor(cv["xy"], cv["xz"], cv["yz"])
+        palette = cv.get("attention_values") if gen.attention_values > 0 else None
+        field = Field.from_generator(gen)
+        assert abs(float(gen.scene_range) - float(dataset_config["scene_range"])) < 1e-12
+        rgb, depth, mask = render_planes(
+            planes, palette, field, height, width, tform_cam2world, focal_length, center, bbox,
+            depth_samples_per_ray, randomize=randomize,
+            white_background=dataset_config["white_background"], fine_sampling=args.fine_sampling,
+            force_no_cam_grad=force_no_cam_grad, zbuffer_depth=zbuffer_depth)
+        return rgb, depth, mask, None, None, model_outputs
+
+    return render

@@ -1,0 +1,256 @@
+"""GPU parity tests: the sm_100a kernels, called through the C ABI (ctypes -> libnfi_b200.so), against
+(1) the stored outputs of the unmodified reference (tests/golden/*.npz) and (2) the CPU oracle on
+seeded synthetic inputs.  Contract (BASELINE.json north_star): bit-exact ray / sample indices;
+rgb, depth, mask and gradients within 1e-4 relative (max-abs-diff / max-abs-ref) in fp32.
+"""
+import pytest
+import torch
+
+import nfi_oracle as O
+from golden_io import (NEARFAR_RANGE, RAY_VARIANTS, RENDER_CASES, eq_bits, load, rel_err,
+                       render_case)
+
+pytestmark = pytest.mark.gpu
+TOL = 1e-4     # the fp32 tolerance of north_star
+
+
+def cu(t):
+    return None if t is None else t.cuda()
+
+
+@pytest.fixture(scope="module")
+def nfi():
+    import nfi_b200
+    from nfi_b200 import _lib, decoder, nerf_utils, ops, render, synth
+    _lib.lib()     # fails loudly if the CUDA library is missing
+    import types
+    return types.SimpleNamespace(ops=ops, nu=nerf_utils, dec=decoder, render=render, synth=synth)
+
+
+@pytest.fixture(scope="module")
+def fn():
+    return load("functions")
+
+
+# ---------------------------------------------------------------- A1
+@pytest.mark.parametrize("variant", sorted(RAY_VARIANTS))
+def test_rays_bitexact(nfi, fn, variant):
+    cam_key, persp, bb, c = RAY_VARIANTS[variant]
+    H, W = [int(v) for v in fn["HW"]]
+    o, d = nfi.nu.get_ray_bundle(H, W, cu(fn["focal"]) if persp else None, cu(fn[cam_key]),
+                                 cu(fn["bbox"]) if bb else None, cu(fn["center"]) if c else None)
+    assert eq_bits(o.cpu(), fn["rays_o_" + variant].expand_as(fn["rays_d_" + variant]))
+    assert eq_bits(d.cpu(), fn["rays_d_" + variant])
+
+
+def test_rays_scalar_focal(nfi, fn):
+    H, W = [int(v) for v in fn["HW"]]
+    _, d = nfi.nu.get_ray_bundle(H, W, cu(fn["focal"][0]), cu(fn["cam_persp"][:1]), None,
+                                 cu(fn["center"][:1]))
+    assert eq_bits(d.cpu(), fn["rays_d_persp_scalar_focal"])
+
+
+@pytest.mark.parametrize("kind", ["persp", "ortho", "cub"])
+def test_rays_backward(nfi, fn, kind):
+    cam_key, persp, _, _ = RAY_VARIANTS[kind]
+    H, W = [int(v) for v in fn["HW"]]
+    cam = fn[cam_key].clone().requires_grad_()
+    focal = fn["focal"].clone().requires_grad_() if persp else None
+    o, d = O.pixel_rays(H, W, cam, focal, fn["center"] if persp else None)
+    d = O.unit_directions(d)
+    g = torch.Generator().manual_seed(5)
+    go, gd = torch.randn(o.expand_as(d).shape, generator=g), torch.randn(d.shape, generator=g)
+    ref = torch.autograd.grad((o.expand_as(d) * go).sum() + (d * gd).sum(), [cam] + ([focal] if persp else []))
+    cam2 = cu(fn[cam_key]).requires_grad_()
+    focal2 = cu(fn["focal"]).requires_grad_() if persp else None
+    o2, d2 = nfi.ops.ray_bundle(H, W, focal2, cam2, None, cu(fn["center"]) if persp else None, normalize=True)
+    got = torch.autograd.grad((o2 * cu(go)).sum() + (d2 * cu(gd)).sum(), [cam2] + ([focal2] if persp else []))
+    for a, b in zip(got, ref):
+        assert rel_err(a.cpu(), b) < TOL
+
+
+# ---------------------------------------------------------------- A2, A3
+@pytest.mark.parametrize("variant", sorted(NEARFAR_RANGE))
+def test_near_far_bitexact(nfi, fn, variant):
+    cam_key, persp, _, _ = RAY_VARIANTS[variant]
+    H, W = [int(v) for v in fn["HW"]]
+    o, d = nfi.ops.ray_bundle(H, W, cu(fn["focal"]) if persp else None, cu(fn[cam_key]), None, None,
+                              normalize=True)
+    assert eq_bits(d.cpu(), fn["unit_d_" + variant])
+    n, f = nfi.nu.compute_near_far_planes(o, d, NEARFAR_RANGE[variant])
+    assert eq_bits(n.cpu(), fn["near_" + variant]) and eq_bits(f.cpu(), fn["far_" + variant])
+
+
+def test_near_far_all_miss_raises(nfi):
+    o = torch.tensor([[0.0, 0.0, 5.0]] * 7).cuda()
+    d = torch.tensor([[0.0, 0.0, 1.0]] * 7).cuda()
+    with pytest.raises(RuntimeError):
+        nfi.nu.compute_near_far_planes(o, d, 1.0)
+    # axis-aligned directions (exact zeros -> +-inf reciprocals) that hit
+    o = torch.tensor([[0.2, -0.3, 3.0], [0.0, 0.0, 3.0], [2.0, 0.0, 3.0]])
+    d = torch.tensor([[0.0, 0.0, -1.0]] * 3)
+    n_ref, f_ref = O.box_near_far(o, d, 1.4)
+    n, f = nfi.nu.compute_near_far_planes(o.cuda(), d.cuda(), 1.4)
+    assert eq_bits(n.cpu(), n_ref) and eq_bits(f.cpu(), f_ref)
+
+
+def test_stratified_bitexact(nfi, fn):
+    n, f = cu(fn["near_persp"]), cu(fn["far_persp"])
+    assert eq_bits(nfi.ops.stratified(n, f, 64, False).cpu(), fn["strat_z_det"])
+    z = nfi.ops.stratified(n, f, 64, True, cu(fn["strat_u"]))
+    assert eq_bits(z.cpu(), fn["strat_z_rand"])
+    H, W = [int(v) for v in fn["HW"]]
+    o, d = nfi.ops.ray_bundle(H, W, cu(fn["focal"]), cu(fn["cam_persp"]), None, None, normalize=True)
+    assert eq_bits(nfi.ops.points_on_rays(o, d, z).cpu(), fn["strat_pts_rand"])
+
+
+def test_stratified_philox_statistics(nfi, fn):
+    """perf mode (no uniforms passed): in-kernel Philox jitter is uniform in [0, 1) per stratum."""
+    n, f = cu(fn["near_persp"]), cu(fn["far_persp"])
+    z0 = nfi.ops.stratified(n, f, 64, False)
+    z = nfi.ops.stratified(n, f, 64, True, None, seed=1234, offset=7)
+    t = ((z - z0) / ((f - n) / 64).unsqueeze(-1)).flatten()
+    assert float(t.min()) >= 0.0 and float(t.max()) < 1.0 + 1e-4
+    assert abs(float(t.mean()) - 0.5) < 5e-3 and abs(float(t.var()) - 1 / 12) < 5e-3
+    z2 = nfi.ops.stratified(n, f, 64, True, None, seed=1234, offset=7)
+    assert eq_bits(z.cpu(), z2.cpu())
+
+
+# ---------------------------------------------------------------- A7, A8
+def test_weights_smoothing_pdf_bitexact(nfi, fn):
+    sg, zz, dd = cu(fn["w_sigma"]), cu(fn["w_z"]), cu(fn["w_dirs"])
+    w = nfi.nu.render_volume_density_weights_only(sg, None, dd, zz)
+    assert eq_bits(w.cpu(), fn["w_weights"])
+    ws = nfi.ops.weights_only(sg, dd, zz, smooth=True)
+    assert eq_bits(ws.cpu(), fn["w_smooth"])
+    mid = 0.5 * (zz[..., 1:] + zz[..., :-1])
+    mid = mid.reshape(-1, mid.shape[-1])
+    wsel = ws.reshape(-1, ws.shape[-1])[..., 1:-1]
+    zr, inds = nfi.ops.sample_pdf(mid, wsel, 64, cu(fn["pdf_u"]), return_indices=True)
+    assert eq_bits(zr.cpu(), fn["pdf_z_rand"])
+    _, ref_inds, _, _ = O.inverse_cdf_samples(mid.cpu(), wsel.cpu(), 64, fn["pdf_u"], return_indices=True)
+    assert bool((inds.cpu().long() == ref_inds).all())          # bit-exact sample indices
+    assert eq_bits(nfi.ops.sample_pdf(mid, wsel, 64, None).cpu(), fn["pdf_z_det"])
+    # the fused importance kernel = the three calls above
+    zf = nfi.ops.importance(sg, dd, zz, cu(fn["pdf_u"]))
+    assert eq_bits(zf.reshape(-1, 64).cpu(), fn["pdf_z_rand"])
+
+
+def test_cumprod_exclusive(nfi):
+    x = torch.rand(37, 200, generator=torch.Generator().manual_seed(3)) * 0.2 + 0.85
+    ref = torch.cumprod(x.double(), -1).roll(1, -1)
+    ref[..., 0] = 1
+    assert rel_err(nfi.nu.cumprod_exclusive(x.cuda()).cpu(), ref.float()) < 1e-6
+
+
+# ---------------------------------------------------------------- A10
+@pytest.mark.parametrize("white", [0, 1])
+def test_composite(nfi, fn, white):
+    sig = cu(fn["c_sigma"]).requires_grad_()
+    col = cu(fn["c_rgb"]).requires_grad_()
+    dirs = cu(fn["c_dirs"]).requires_grad_()
+    sem = cu(fn["c_sem"]).requires_grad_()
+    out = nfi.nu.render_volume_density(sig, col, None, dirs, cu(fn["c_z"]), cu(fn["c_nrm"]), sem,
+                                       white_background=bool(white))
+    for k, v in zip(("rgb", "depth", "mask", "nrm", "sem"), out):
+        assert rel_err(v.cpu(), fn["c%d_%s" % (white, k)]) < 1e-5, k
+    gs, gc, gd = torch.autograd.grad((out[0] * cu(fn["c_grad_rgb"])).sum() + (out[2] * cu(fn["c_grad_mask"])).sum(),
+                                     (sig, col, dirs))
+    assert rel_err(gs.cpu(), fn["c%d_dsigma" % white]) < TOL
+    assert rel_err(gc.cpu(), fn["c%d_drgb" % white]) < TOL
+    assert rel_err(gd.cpu(), fn["c%d_ddirs" % white]) < TOL
+
+
+def test_composite_semantics_backward(nfi, fn):
+    g = torch.Generator().manual_seed(11)
+    sig = fn["c_sigma"].clone().requires_grad_()
+    col = fn["c_rgb"].clone().requires_grad_()
+    sem = fn["c_sem"].clone().requires_grad_()
+    dn = O.vec3_norm(fn["c_dirs"])
+    out = O.composite(sig, col, fn["c_z"], dn, False, None, sem)
+    gsem = torch.randn(out[4].shape, generator=g)
+    ref = torch.autograd.grad((out[4] * gsem).sum() + out[0].sum(), (sig, sem))
+    sig2, col2, sem2 = cu(fn["c_sigma"]).requires_grad_(), cu(fn["c_rgb"]).requires_grad_(), cu(fn["c_sem"]).requires_grad_()
+    out2 = nfi.ops.composite(sig2, col2, cu(fn["c_dirs"]), cu(fn["c_z"]), None, sem2, False)
+    got = torch.autograd.grad((out2[4] * cu(gsem)).sum() + out2[0].sum(), (sig2, sem2))
+    for a, b in zip(got, ref):
+        assert rel_err(a.cpu(), b) < TOL
+
+
+# ---------------------------------------------------------------- A4-A6
+def _field(nfi, g, A, use_sdf, dev="cuda", grad=False):
+    mk = (lambda t: t.clone().to(dev).requires_grad_()) if grad else (lambda t: t.to(dev))
+    return nfi.dec.Field(mk(g["W0"]), mk(g["b0"]), mk(g["W1"]), mk(g["b1"]),
+                         mk(g["beta"]) if use_sdf else None, mk(g["alpha"]) if use_sdf else None,
+                         1.4, A, use_sdf)
+
+
+@pytest.mark.parametrize("name,A,use_sdf", [("sdf_attn", 10, True), ("density_rgb", 0, False)])
+def test_decoder_and_heads(nfi, name, A, use_sdf):
+    g = load("decoder_" + name)
+    B, res = g["planes"].shape[0], g["planes"].shape[-1]
+    planes = cu(g["planes"]).requires_grad_()
+    pts = cu(g["pts"]).requires_grad_()
+    fld = _field(nfi, g, A, use_sdf)
+    # raw decoder (TriplanarDecoder.forward): coords are in box units
+    pcl = nfi.ops.planes_to_channels_last(planes)
+    cfg_raw = nfi.ops.FieldConfig(A, False, 1.0)
+    y, _ = nfi.ops.field_on_points(pcl, None, fld.W0, fld.b0, fld.W1, fld.b1, None, None, pts / 1.4,
+                                   cfg_raw, mode=1)
+    assert rel_err(y.cpu(), g["y"]) < TOL
+    gd = torch.autograd.grad((y * cu(g["gy"])).sum(), [planes, pts])
+    assert rel_err(gd[0].cpu(), g["dy_planes"]) < TOL
+    assert rel_err(gd[1].cpu(), g["dy_pts"]) < TOL
+    # heads
+    fld = _field(nfi, g, A, use_sdf, grad=True)
+    pal = cu(g["palette"]).requires_grad_() if A > 0 else None
+    o4, probs = nfi.ops.field_on_points(pcl, pal, *fld.tensors(), pts, fld.cfg, mode=0, want_probs=True)
+    sigma, rgb = o4[..., 0], o4[..., 1:]
+    assert rel_err(sigma.cpu(), g["sigma"]) < TOL and rel_err(rgb.cpu(), g["rgb"]) < TOL
+    if A > 0:
+        assert rel_err(probs.cpu(), g["semantics"]) < TOL
+    leaves = [planes, pts] + ([pal] if A > 0 else []) + ([fld.beta, fld.alpha] if use_sdf else [])
+    keys = ["ds_planes", "ds_pts"] + (["ds_palette"] if A > 0 else []) + (["ds_beta", "ds_alpha"] if use_sdf else [])
+    gs = torch.autograd.grad((sigma * cu(g["gsigma"])).sum() + (rgb * cu(g["grgb"])).sum(), leaves)
+    for a, k in zip(gs, keys):
+        assert rel_err(a.cpu(), g[k]) < TOL, k
+
+
+def test_sampler_dropin(nfi):
+    g = load("decoder_sdf_attn")
+    fld = _field(nfi, g, 10, True)
+    smp = nfi.dec.make_sampler(cu(g["planes"]), cu(g["palette"]), fld)
+    out = smp(cu(g["pts"]).unsqueeze(2), ["sigma", "rgb", "semantics", "sdf_distance"])
+    assert rel_err(out["sigma"].cpu(), g["sigma"]) < TOL and rel_err(out["rgb"].cpu(), g["rgb"]) < TOL
+    assert rel_err(out["semantics"].cpu(), g["semantics"]) < TOL
+    assert rel_err(out["sdf_distance"].cpu(), g["y"][..., :1]) < TOL
+
+
+# ---------------------------------------------------------------- A11: the whole render
+def _run_render(nfi, g, c, planes, pal, cam, focal):
+    fld = nfi.dec.Field(cu(g["W0"]), cu(g["b0"]), cu(g["W1"]), cu(g["b1"]), cu(g["beta"]), cu(g["alpha"]),
+                        c["scene_range"], 10, True)
+    return nfi.render.render_planes(
+        planes, pal, fld, c["H"], c["W"], cam, focal, cu(g.get("center")), None, c["S"],
+        randomize=c["randomize"], white_background=c["white"], fine_sampling=True,
+        force_no_cam_grad=c["no_cam"], zbuffer_depth=c["zbuffer"], u_strat=cu(g.get("u_strat")),
+        u_pdf=cu(g.get("u_pdf")), return_aux=True)
+
+
+@pytest.mark.parametrize("name", RENDER_CASES)
+def test_render_golden(nfi, name):
+    g = render_case(name)
+    c = g["cfg"]
+    B = g["planes"].shape[0]
+    planes = cu(g["planes"]).requires_grad_()
+    pal = cu(g["palette"]).requires_grad_()
+    cam = cu(g["cam"]).requires_grad_()
+    focal = cu(g["focal"]).requires_grad_() if c["persp"] else None
+    rgb, depth, mask, aux = _run_render(nfi, g, c, planes, pal, cam, focal)
+    assert rel_err(rgb.cpu(), g["rgb"]) < TOL and rel_err(depth.cpu(), g["depth"]) < TOL
+    assert rel_err(mask.cpu(), g["mask"]) < TOL
+    loss = (rgb - cu(g["target"])).abs().mean() * B + (mask * cu(g["gmask"])).mean()
+    wants = [planes, pal] + ([] if c["no_cam"] else [cam] + ([focal] if c["persp"] else []))
+    keys = ["d_planes", "d_palette"] + ([] if c["no_cam"] else ["d_cam"] + (["d_focal"] if c["persp"] else []))
+    for a, k in zip(torch.autograd.grad(loss, wants), keys):
+        assert rel_err(a.cpu(), g[k]) < TOL, k
