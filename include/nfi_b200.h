@@ -117,6 +117,12 @@ int nfi_field_bwd(const NfiField* field, const float* planes_cl, const float* pa
                   const float* g_out, float* g_planes_cl, float* g_palette, float* g_points,
                   float* g_params, nfi_stream_t stream);
 
+/* ---- decoder MLP alone (models/generator.py:295-299, 329-330; EqualizedLinear gains applied
+ *      inside): feat [n,32] -> y [n, n_out] on tcgen05 tensor cores (3xTF32 split, fp32
+ *      accumulate in TMEM).  hpre [n,64] (optional) receives the hidden pre-activations. --------- */
+int nfi_decoder_mlp_fwd(const NfiField* field, const float* feat, int64_t n, float* y, float* hpre,
+                        nfi_stream_t stream);
+
 /* ---- A7: render_volume_density_weights_only (lib/nerf_utils.py:166-182) + EG3D smoothing
  *      (run.py:266-272, smooth != 0).  sigma is read with stride `sigma_stride` floats. ----------- */
 int nfi_weights_only(const float* sigma, int sigma_stride, const float* dirs, const float* z,

@@ -1,0 +1,139 @@
+// Decoder MLP on tcgen05 (3xTF32, fp32 accumulate in TMEM): per-CTA state + the tile routines that
+// the standalone MLP kernel (nfi_mlp.cu) and the fused field kernels share.
+//
+// One tile = 128 samples = the 128 TMEM lanes of one CTA (UMMA M = 128, cta_group::1).
+//   layer 0 : D0[128 x 64]  = F[128 x 32] . W0s^T          A = features in shared memory (SS)
+//   epilogue: H = softplus(D0 + b0) -> written back to TMEM as the next A operand (hi / lo)
+//   layer 1 : D1[128 x 16]  = H[128 x 64] . W1s^T          A = TMEM (TS), B = shared memory
+// TMEM columns: [0,64) D0 | [64,128) H_hi | [128,192) H_lo | [192,208) D1  (+ backward, see below)
+#pragma once
+#include "nfi_math.cuh"
+#include "nfi_tc.cuh"
+
+namespace nfi_mlp {
+
+constexpr int kTile = 128;
+constexpr int kC = 32, kH = 64, kY = 16;
+constexpr uint32_t kSBO = 128;
+constexpr uint32_t kLboA = 128 * 16 + 16;    // feature tile: +16 B pad -> conflict-free 8-lane float4 stores
+constexpr uint32_t kLboW0 = kH * 16;         // W0s: 64 rows (N) x 32 (K)
+constexpr uint32_t kLboW1 = kY * 16;         // W1s: 16 rows (N) x 64 (K)
+constexpr uint32_t kLboW1t = kH * 16;        // W1s^T: 64 rows (N) x 16 (K)      (backward: dH = dY . W1s)
+constexpr uint32_t kLboW0t = kC * 16;        // W0s^T: 32 rows (N) x 64 (K)      (backward: dF = dHpre . W0s)
+constexpr int kColD0 = 0, kColHhi = 64, kColHlo = 128, kColD1 = 192;
+constexpr int kTmemCols = 256;
+
+struct Operands {                        // all offsets 16-byte aligned
+  float a_hi[8 * kLboA / 4];             // feature tile, hi parts     [chunk][row][4]
+  float a_lo[8 * kLboA / 4];
+  float w0_hi[kH * kC], w0_lo[kH * kC];  // [k/4][n][4]
+  float w1_hi[kY * kH], w1_lo[kY * kH];  // [k/4][n][4]
+  float b0[kH];
+  float b1[kY];
+  uint64_t bar;
+  uint32_t tmem_base;
+  uint32_t pad;
+};
+
+// gain-scaled EqualizedLinear weights (models/stylegan.py:170-177) -> hi / lo operand tiles
+__device__ __forceinline__ void load_weights(Operands& s, const float* __restrict__ W0,
+                                             const float* __restrict__ b0, const float* __restrict__ W1,
+                                             const float* __restrict__ b1, int n_out) {
+  const float g0 = (float)(1.0 / sqrt((double)kC));
+  const float g1 = (float)(1.0 / sqrt((double)kH));
+  for (int i = threadIdx.x; i < kH * kC; i += blockDim.x) {
+    const int n = i / kC, k = i % kC;                       // W0 is [64][32]
+    const float w = NFI_MUL(W0[i], g0);
+    const int o = (k >> 2) * (kLboW0 / 4) + n * 4 + (k & 3);
+    s.w0_hi[o] = __uint_as_float(nfi_tc::tf32_hi(w));
+    s.w0_lo[o] = nfi_tc::tf32_lo(w);
+  }
+  for (int i = threadIdx.x; i < kY * kH; i += blockDim.x) {
+    const int n = i / kH, k = i % kH;                       // W1 is [n_out][64], zero-padded to 16 rows
+    const float w = n < n_out ? NFI_MUL(W1[i], g1) : 0.f;
+    const int o = (k >> 2) * (kLboW1 / 4) + n * 4 + (k & 3);
+    s.w1_hi[o] = __uint_as_float(nfi_tc::tf32_hi(w));
+    s.w1_lo[o] = nfi_tc::tf32_lo(w);
+  }
+  for (int i = threadIdx.x; i < kH; i += blockDim.x) s.b0[i] = b0[i];
+  for (int i = threadIdx.x; i < kY; i += blockDim.x) s.b1[i] = i < n_out ? b1[i] : 0.f;
+}
+
+// store 4 consecutive channels (chunk c4) of feature row `row` as hi / lo operands
+__device__ __forceinline__ void store_feat4(Operands& s, int row, int c4, float4 v) {
+  const int o = c4 * (kLboA / 4) + row * 4;
+  const uint32_t hx = nfi_tc::tf32_hi(v.x), hy = nfi_tc::tf32_hi(v.y), hz = nfi_tc::tf32_hi(v.z), hw = nfi_tc::tf32_hi(v.w);
+  *reinterpret_cast<float4*>(&s.a_hi[o]) = make_float4(__uint_as_float(hx), __uint_as_float(hy), __uint_as_float(hz), __uint_as_float(hw));
+  *reinterpret_cast<float4*>(&s.a_lo[o]) = make_float4(v.x - __uint_as_float(hx), v.y - __uint_as_float(hy),
+                                                       v.z - __uint_as_float(hz), v.w - __uint_as_float(hw));
+}
+
+// Issue layer 0 (12 MMAs, K = 32) -- ONE thread.  D0 <- F . W0s^T
+__device__ __forceinline__ void issue_layer0(const Operands& s, uint32_t tmem) {
+  const uint32_t idesc = nfi_tc::idesc_tf32(kTile, kH);
+  const uint32_t a_hi = nfi_tc::smem_u32(s.a_hi), a_lo = nfi_tc::smem_u32(s.a_lo);
+  const uint32_t b_hi = nfi_tc::smem_u32(s.w0_hi), b_lo = nfi_tc::smem_u32(s.w0_lo);
+  uint32_t acc = 0;
+#pragma unroll
+  for (int j = 0; j < kC / 8; ++j) {
+    const uint64_t ah = nfi_tc::smem_desc(a_hi + 2 * j * kLboA, kLboA, kSBO);
+    const uint64_t al = nfi_tc::smem_desc(a_lo + 2 * j * kLboA, kLboA, kSBO);
+    const uint64_t bh = nfi_tc::smem_desc(b_hi + 2 * j * kLboW0, kLboW0, kSBO);
+    const uint64_t bl = nfi_tc::smem_desc(b_lo + 2 * j * kLboW0, kLboW0, kSBO);
+    nfi_tc::mma_tf32_ss(tmem + kColD0, al, bh, idesc, acc); acc = 1;     // small terms first
+    nfi_tc::mma_tf32_ss(tmem + kColD0, ah, bl, idesc, 1);
+    nfi_tc::mma_tf32_ss(tmem + kColD0, ah, bh, idesc, 1);
+  }
+}
+
+// Issue layer 1 (24 MMAs, K = 64) -- ONE thread.  D1 <- H . W1s^T with H (hi, lo) in TMEM
+__device__ __forceinline__ void issue_layer1(const Operands& s, uint32_t tmem) {
+  const uint32_t idesc = nfi_tc::idesc_tf32(kTile, kY);
+  const uint32_t b_hi = nfi_tc::smem_u32(s.w1_hi), b_lo = nfi_tc::smem_u32(s.w1_lo);
+  uint32_t acc = 0;
+#pragma unroll
+  for (int j = 0; j < kH / 8; ++j) {
+    const uint64_t bh = nfi_tc::smem_desc(b_hi + 2 * j * kLboW1, kLboW1, kSBO);
+    const uint64_t bl = nfi_tc::smem_desc(b_lo + 2 * j * kLboW1, kLboW1, kSBO);
+    nfi_tc::mma_tf32_ts(tmem + kColD1, tmem + kColHlo + 8 * j, bh, idesc, acc); acc = 1;
+    nfi_tc::mma_tf32_ts(tmem + kColD1, tmem + kColHhi + 8 * j, bl, idesc, 1);
+    nfi_tc::mma_tf32_ts(tmem + kColD1, tmem + kColHhi + 8 * j, bh, idesc, 1);
+  }
+}
+
+// softplus with the reference's threshold (torch.nn.Softplus: beta = 1, threshold = 20)
+__device__ __forceinline__ float softplus_f(float x) { return x > 20.f ? x : log1pf(expf(x)); }
+
+// Epilogue 0, executed by all 128 threads: D0 row -> H = softplus(D0 + b0) -> TMEM (hi, lo).
+// hpre (optional, 64 floats per thread) keeps the pre-activation for the backward.
+template <bool KEEP>
+__device__ __forceinline__ void epilogue0(const Operands& s, uint32_t tmem_lane, float* hpre) {
+#pragma unroll
+  for (int q = 0; q < kH / 16; ++q) {
+    float v[16];
+    nfi_tc::tmem_ld16(tmem_lane + kColD0 + 16 * q, v);
+    nfi_tc::tmem_ld_wait();
+    uint32_t hi[16], lo[16];
+#pragma unroll
+    for (int i = 0; i < 16; ++i) {
+      const float pre = v[i] + s.b0[16 * q + i];
+      if (KEEP) hpre[16 * q + i] = pre;
+      const float h = softplus_f(pre);
+      hi[i] = nfi_tc::tf32_hi(h);
+      lo[i] = __float_as_uint(h - __uint_as_float(hi[i]));
+    }
+    nfi_tc::tmem_st16(tmem_lane + kColHhi + 16 * q, hi);
+    nfi_tc::tmem_st16(tmem_lane + kColHlo + 16 * q, lo);
+  }
+  nfi_tc::tmem_st_wait();
+}
+
+// Epilogue 1: y[16] = D1 row + b1
+__device__ __forceinline__ void epilogue1(const Operands& s, uint32_t tmem_lane, float (&y)[16]) {
+  nfi_tc::tmem_ld16(tmem_lane + kColD1, y);
+  nfi_tc::tmem_ld_wait();
+#pragma unroll
+  for (int i = 0; i < 16; ++i) y[i] += s.b1[i];
+}
+
+}  // namespace nfi_mlp

@@ -261,6 +261,18 @@ class _Field(Function):
                 None, None, None, None, None)
 
 
+def decoder_mlp(feat, W0, b0, W1, b1, want_hidden=False):
+    """Decoder MLP alone on the tensor cores (forward only): feat [n,32] -> y [n,n_out]."""
+    ft = f32c(feat.detach())
+    n = ft.shape[0]
+    n_out = W1.shape[0]
+    field, keep = _lib.make_field_struct(W0, b0, W1, b1, None, None, n_out - 1 if n_out != 4 else 0, False, 1.0)
+    y = _empty(ft, n, n_out)
+    hp = _empty(ft, n, 64) if want_hidden else None
+    call("nfi_decoder_mlp_fwd", ft, field, ptr(ft), n, ptr(y), ptr(hp))
+    return (y, hp) if want_hidden else y
+
+
 def field_on_rays(planes_cl, palette, W0, b0, W1, b1, beta, alpha, origins, dirs, z, cfg,
                   img_w=0, skip_oob=False, want_probs=False):
     """(sigma, r, g, b) [.., S, 4] for the samples o + d*z of every ray (no points tensor in HBM)."""
