@@ -49,7 +49,7 @@ decoder_mlp_fwd_kernel(const float* __restrict__ W0, const float* __restrict__ b
     nfi_tc::mbar_wait(&s.bar, parity); parity ^= 1;
     nfi_tc::fence_after_sync();
     float hpre[kH];
-    epilogue0<true>(s, tmem_lane, hpre);
+    epilogue0<4, true>(s, tmem_lane, 0, hpre);
     nfi_tc::fence_before_sync();
     __syncthreads();
     if (tid == 0) {

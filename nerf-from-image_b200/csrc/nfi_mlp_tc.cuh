@@ -104,26 +104,26 @@ __device__ __forceinline__ void issue_layer1(const Operands& s, uint32_t tmem) {
 // softplus with the reference's threshold (torch.nn.Softplus: beta = 1, threshold = 20)
 __device__ __forceinline__ float softplus_f(float x) { return x > 20.f ? x : log1pf(expf(x)); }
 
-// Epilogue 0, executed by all 128 threads: D0 row -> H = softplus(D0 + b0) -> TMEM (hi, lo).
-// hpre (optional, 64 floats per thread) keeps the pre-activation for the backward.
-template <bool KEEP>
-__device__ __forceinline__ void epilogue0(const Operands& s, uint32_t tmem_lane, float* hpre) {
+// Epilogue 0 for 16*NQ hidden columns starting at col0 of this thread's TMEM lane:
+// D0 -> H = softplus(D0 + b0) -> TMEM (hi, lo).  hpre (optional) keeps the pre-activations.
+template <int NQ, bool KEEP>
+__device__ __forceinline__ void epilogue0(const Operands& s, uint32_t tmem_lane, int col0, float* hpre) {
 #pragma unroll
-  for (int q = 0; q < kH / 16; ++q) {
+  for (int q = 0; q < NQ; ++q) {
     float v[16];
-    nfi_tc::tmem_ld16(tmem_lane + kColD0 + 16 * q, v);
+    nfi_tc::tmem_ld16(tmem_lane + kColD0 + col0 + 16 * q, v);
     nfi_tc::tmem_ld_wait();
     uint32_t hi[16], lo[16];
 #pragma unroll
     for (int i = 0; i < 16; ++i) {
-      const float pre = v[i] + s.b0[16 * q + i];
+      const float pre = v[i] + s.b0[col0 + 16 * q + i];
       if (KEEP) hpre[16 * q + i] = pre;
       const float h = softplus_f(pre);
       hi[i] = nfi_tc::tf32_hi(h);
       lo[i] = __float_as_uint(h - __uint_as_float(hi[i]));
     }
-    nfi_tc::tmem_st16(tmem_lane + kColHhi + 16 * q, hi);
-    nfi_tc::tmem_st16(tmem_lane + kColHlo + 16 * q, lo);
+    nfi_tc::tmem_st16(tmem_lane + kColHhi + col0 + 16 * q, hi);
+    nfi_tc::tmem_st16(tmem_lane + kColHlo + col0 + 16 * q, lo);
   }
   nfi_tc::tmem_st_wait();
 }
