@@ -1,16 +1,263 @@
-// Backward entry point of the triplane field kernels (kernels are instantiated in
-// nfi_field_bwd_heads.cu / nfi_field_bwd_raw.cu so that the translation units build in parallel).
-#include "nfi_field_host.cuh"
+// Backward of the fused triplane field (see nfi_field_tc.cuh for the tiling).  Nothing but the
+// 16-byte upstream gradient per sample is read: the forward (gather, MLP, heads) is recomputed per
+// tile, the MLP adjoint runs on tcgen05 (nfi_mlp_tc.cuh), and the feature gradient is scattered
+// into the channels-last gradient planes with red.global.add.v4.f32 (one 128-byte line per texel
+// and 8 lanes).  Summation order into the planes is not deterministic (fp32 atomics).
+#include "nfi_field_tc_host.cuh"
 
-void nfi_field_bwd_launch_heads(const nfi_field::Args& a, int grid, cudaStream_t st);
-void nfi_field_bwd_launch_raw(const nfi_field::Args& a, int grid, cudaStream_t st);
+namespace nfi_ftc {
+
+__device__ __forceinline__ void red_add_v4(float* addr, float a, float b, float c, float d) {
+  asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(addr), "f"(a), "f"(b), "f"(c), "f"(d)
+               : "memory");
+}
+
+constexpr int kDfLd = 36;            // d feature tile row stride (floats): conflict-free float4 rows
+constexpr int kNPal = 3 * (NFI_YPAD - 1);
+
+struct BwdSmem {
+  nfi_mlp::Operands op;              // op.a_hi / a_lo double as the d feature tile after layer 0
+  nfi_mlp::BwdWeights bw;
+  Tables t;
+  float act[kTile];
+};
+static_assert(kTile * kDfLd <= 2 * 8 * (int)nfi_mlp::kLboA / 4, "d feature tile does not fit the operand tile");
+
+// scatter d feat into the gradient planes; optionally d/d point from the re-read texels
+template <bool WANT_PTS>
+__device__ __forceinline__ void phase4_scatter(const Args& a, const Tables& t, const float* act,
+                                               const float* dft, int b, int64_t tt) {
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int c4 = lane & 7;
+  const float third = 1.f / 3.f;
+  const int64_t plane_f4 = (int64_t)a.Hp * a.Wp * 8;
+#pragma unroll 1
+  for (int it = 0; it < 4; ++it) {
+    const int s = warp * 16 + it * 4 + (lane >> 3);
+    float gp[3] = {0.f, 0.f, 0.f};
+    if (act[s] > 0.5f) {
+      float4 g = *reinterpret_cast<const float4*>(&dft[s * kDfLd + c4 * 4]);
+      g.x *= third; g.y *= third; g.z *= third; g.w *= third;
+      const int64_t img_f4 = (int64_t)b * 3 * plane_f4 + c4;
+#pragma unroll
+      for (int p = 0; p < 3; ++p) {
+        const int4 o = t.toff[p][s];
+        const float4 w = t.twgt[p][s];
+        const int64_t base = img_f4 + p * plane_f4;
+        if (a.g_planes) {
+          // a clamped neighbour (x1 == x0 at the border) carries weight 0: adding 0 is harmless
+          float* G = a.g_planes;
+          red_add_v4(G + (base + o.x) * 4, g.x * w.x, g.y * w.x, g.z * w.x, g.w * w.x);
+          red_add_v4(G + (base + o.y) * 4, g.x * w.y, g.y * w.y, g.z * w.y, g.w * w.y);
+          red_add_v4(G + (base + o.z) * 4, g.x * w.z, g.y * w.z, g.z * w.z, g.w * w.z);
+          red_add_v4(G + (base + o.w) * 4, g.x * w.w, g.y * w.w, g.z * w.w, g.w * w.w);
+        }
+        if (WANT_PTS) {
+          const float4* P = reinterpret_cast<const float4*>(a.planes) + base;
+          const float4 v00 = __ldg(P + o.x), v01 = __ldg(P + o.y), v10 = __ldg(P + o.z), v11 = __ldg(P + o.w);
+          const float4 d = t.tder[p][s];              // tx, ty, d ix / d x, d iy / d x
+          // d/d ix = sum_c g_c ((v01 - v00)(1 - ty) + (v11 - v10) ty); d/d iy likewise
+          const float ax = (v01.x - v00.x) * g.x + (v01.y - v00.y) * g.y + (v01.z - v00.z) * g.z + (v01.w - v00.w) * g.w;
+          const float bx = (v11.x - v10.x) * g.x + (v11.y - v10.y) * g.y + (v11.z - v10.z) * g.z + (v11.w - v10.w) * g.w;
+          const float ay = (v10.x - v00.x) * g.x + (v10.y - v00.y) * g.y + (v10.z - v00.z) * g.z + (v10.w - v00.w) * g.w;
+          const float by = (v11.x - v01.x) * g.x + (v11.y - v01.y) * g.y + (v11.z - v01.z) * g.z + (v11.w - v01.w) * g.w;
+          const float gx = fmaf(bx - ax, d.y, ax), gy = fmaf(by - ay, d.x, ay);
+          gp[nfi_plane_axis_a(p)] = fmaf(gx, d.z, gp[nfi_plane_axis_a(p)]);
+          gp[nfi_plane_axis_b(p)] = fmaf(gy, d.w, gp[nfi_plane_axis_b(p)]);
+        }
+      }
+    }
+    if (WANT_PTS) {
+#pragma unroll
+      for (int c = 0; c < 3; ++c) {
+        gp[c] += __shfl_xor_sync(0xffffffffu, gp[c], 1);
+        gp[c] += __shfl_xor_sync(0xffffffffu, gp[c], 2);
+        gp[c] += __shfl_xor_sync(0xffffffffu, gp[c], 4);
+      }
+      if (c4 == 0 && t.keep[s] != -1.f) {
+        const int64_t id = sample_id(a, b, tt, s);
+        const float inv_r = 1.f / a.f.scene_range;
+        a.g_points[id * 3 + 0] = gp[0] * inv_r;
+        a.g_points[id * 3 + 1] = gp[1] * inv_r;
+        a.g_points[id * 3 + 2] = gp[2] * inv_r;
+      }
+    }
+  }
+}
+
+template <bool PTS, int MODE, bool WANT_PTS>
+__global__ void __launch_bounds__(kThreads, 2)
+field_bwd_tc_kernel(const Args a) {
+  extern __shared__ __align__(128) unsigned char smem_raw[];
+  BwdSmem& sm = *reinterpret_cast<BwdSmem*>(smem_raw);
+  nfi_mlp::Operands& op = sm.op;
+  Tables& t = sm.t;
+  float* dft = op.a_hi;
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  nfi_mlp::load_weights(op, a.f.W0, a.f.b0, a.f.W1, a.f.b1, a.f.n_out);
+  nfi_mlp::load_weights_bwd(sm.bw, a.f.W0, a.f.W1, a.f.n_out);
+  if (warp == 0) nfi_tc::tmem_alloc(&op.tmem_base, nfi_mlp::kTmemCols);
+  if (tid == 0) { nfi_tc::mbar_init(&op.bar, 1); nfi_tc::mbar_fence_init(); }
+  nfi_tc::fence_proxy_async();
+  nfi_tc::fence_before_sync();
+  __syncthreads();
+  nfi_tc::fence_after_sync();
+  const uint32_t tmem = op.tmem_base;
+  const uint32_t tmem_lane = tmem + ((uint32_t)((warp & 3) * 32) << 16);
+  const NfiHeads hd = make_heads(a.f);
+  const int npal = 3 * hd.A;
+  const bool want_pal = MODE == 0 && a.g_palette != nullptr;
+  const bool want_par = MODE == 0 && a.g_params != nullptr && hd.use_sdf;
+  uint32_t parity = 0;
+  for (int b = 0; b < a.B; ++b) {
+    int64_t lo, hi;
+    cta_tile_range(a.tiles_per_image, lo, hi);
+    float dpal[kNPal];               // per-thread partial sums over this CTA's tiles of image b
+#pragma unroll
+    for (int q = 0; q < kNPal; ++q) dpal[q] = 0.f;
+    float dbeta = 0.f, dalpha = 0.f;
+    const float* pal = (MODE == 0 && a.palette) ? a.palette + (int64_t)b * npal : nullptr;
+    for (int64_t tt = lo; tt < hi; ++tt) {
+      int64_t id = -1;
+      bool act = false;
+      float gy[NFI_YPAD];
+#pragma unroll
+      for (int o = 0; o < NFI_YPAD; ++o) gy[o] = 0.f;
+      if (tid < kTile) {
+        id = sample_id(a, b, tt, tid);
+        phase1<PTS, MODE, WANT_PTS>(a, t, id, b, tid);
+        if (id >= 0) {
+          if (MODE == 0) {
+            const float4 g = reinterpret_cast<const float4*>(a.g_out)[id];
+            gy[0] = g.x; gy[1] = g.y; gy[2] = g.z; gy[3] = g.w;
+            const bool col = (g.y != 0.f) || (g.z != 0.f) || (g.w != 0.f);
+            // outside the box sigma is masked (generator.py:634): only a colour gradient can act;
+            // samples with an all-zero upstream gradient are skipped exactly
+            act = sample_active(a, t.keep[tid]) && (col || (g.x != 0.f && t.keep[tid] > 0.5f));
+          } else {
+#pragma unroll
+            for (int o = 0; o < NFI_YPAD; ++o) {
+              if (o < a.f.n_out) { gy[o] = a.g_out[id * a.f.n_out + o]; act = act || (gy[o] != 0.f); }
+            }
+          }
+        }
+        sm.act[tid] = act ? 1.f : 0.f;
+        if (!act && t.keep[tid] >= 0.f) t.keep[tid] = -2.f;   // valid sample, nothing to do: no gather
+      }
+      const int any = __syncthreads_or(act ? 1 : 0);
+      if (any) {
+        phase2_gather(a, t, op);
+        nfi_tc::fence_proxy_async();
+        nfi_tc::fence_before_sync();
+        __syncthreads();
+        if (tid == 0) { nfi_tc::fence_after_sync(); nfi_mlp::issue_layer0(op, tmem); nfi_tc::mma_commit(&op.bar); }
+        nfi_tc::mbar_wait(&op.bar, parity); parity ^= 1;
+        nfi_tc::fence_after_sync();
+        nfi_mlp::epilogue0<2, false>(op, tmem_lane, (warp >> 2) * 32, nullptr);
+        nfi_tc::fence_before_sync();
+        __syncthreads();
+        if (tid == 0) { nfi_tc::fence_after_sync(); nfi_mlp::issue_layer1(op, tmem); nfi_tc::mma_commit(&op.bar); }
+        nfi_tc::mbar_wait(&op.bar, parity); parity ^= 1;
+        nfi_tc::fence_after_sync();
+        if (warp < 4) {
+          float dy[NFI_YPAD];
+#pragma unroll
+          for (int o = 0; o < NFI_YPAD; ++o) dy[o] = 0.f;
+          if (MODE == 0) {
+            float y[nfi_mlp::kY];
+            nfi_mlp::epilogue1(op, tmem_lane, y);
+            if (act) {
+              const float keep = t.keep[tid] > 0.5f ? 1.f : 0.f;
+              float sigma, rgb[3], probs[NFI_YPAD - 1];
+              nfi_heads_fwd(hd, y, keep, pal, sigma, rgb, probs);
+              const float drgb[3] = {gy[1], gy[2], gy[3]};
+              nfi_heads_bwd(hd, y, keep, pal, probs, rgb, gy[0], drgb, dy, want_par ? &dbeta : nullptr,
+                            want_par ? &dalpha : nullptr);
+              if (want_pal) {
+#pragma unroll
+                for (int q = 0; q < NFI_YPAD - 1; ++q) {
+                  if (q < hd.A) {
+                    dpal[3 * q] = fmaf(probs[q], drgb[0], dpal[3 * q]);
+                    dpal[3 * q + 1] = fmaf(probs[q], drgb[1], dpal[3 * q + 1]);
+                    dpal[3 * q + 2] = fmaf(probs[q], drgb[2], dpal[3 * q + 2]);
+                  }
+                }
+              }
+            }
+          } else {
+#pragma unroll
+            for (int o = 0; o < NFI_YPAD; ++o) dy[o] = gy[o];
+          }
+          nfi_mlp::store_dy(tmem_lane, dy);
+        }
+        nfi_tc::fence_before_sync();
+        __syncthreads();
+        if (tid == 0) { nfi_tc::fence_after_sync(); nfi_mlp::issue_dh(sm.bw, tmem); nfi_tc::mma_commit(&op.bar); }
+        nfi_tc::mbar_wait(&op.bar, parity); parity ^= 1;
+        nfi_tc::fence_after_sync();
+        nfi_mlp::epilogue2<2>(tmem_lane, (warp >> 2) * 32);
+        nfi_tc::fence_before_sync();
+        __syncthreads();
+        if (tid == 0) { nfi_tc::fence_after_sync(); nfi_mlp::issue_df(sm.bw, tmem); nfi_tc::mma_commit(&op.bar); }
+        nfi_tc::mbar_wait(&op.bar, parity); parity ^= 1;
+        nfi_tc::fence_after_sync();
+        {   // d feature rows -> shared memory (row-major, padded)
+          float v[16];
+          const int col0 = (warp >> 2) * 16;
+          nfi_tc::tmem_ld16(tmem_lane + nfi_mlp::kColDF + col0, v);
+          nfi_tc::tmem_ld_wait();
+          float* row = dft + ((warp & 3) * 32 + lane) * kDfLd + col0;
+#pragma unroll
+          for (int q = 0; q < 4; ++q)
+            *reinterpret_cast<float4*>(row + 4 * q) = make_float4(v[4 * q], v[4 * q + 1], v[4 * q + 2], v[4 * q + 3]);
+        }
+        nfi_tc::fence_before_sync();
+        __syncthreads();
+      }
+      // scatter (+ d/d point); with no active sample this only writes the zero point gradients
+      if (any || WANT_PTS) phase4_scatter<WANT_PTS>(a, t, sm.act, dft, b, tt);
+      __syncthreads();                 // tables and the d feature tile are rewritten by the next tile
+    }
+    // palette / beta / alpha partial sums of this CTA for image b: warp reduce, one atomic per warp
+    if ((want_pal || want_par) && warp < 4 && hi > lo) {
+      if (want_pal) {
+#pragma unroll
+        for (int q = 0; q < kNPal; ++q) {
+          if (q < npal) {
+            float v = dpal[q];
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+            if (lane == 0 && v != 0.f) atomicAdd(&a.g_palette[(int64_t)b * npal + q], v);
+          }
+        }
+      }
+      if (want_par) {
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+          dbeta += __shfl_xor_sync(0xffffffffu, dbeta, o);
+          dalpha += __shfl_xor_sync(0xffffffffu, dalpha, o);
+        }
+        const int base = NFI_HID * NFI_C + NFI_HID + a.f.n_out * NFI_HID + a.f.n_out;
+        if (lane == 0) {
+          if (dbeta != 0.f) atomicAdd(&a.g_params[base], dbeta);
+          if (dalpha != 0.f) atomicAdd(&a.g_params[base + 1], dalpha);
+        }
+      }
+    }
+  }
+  __syncthreads();
+  if (warp == 0) nfi_tc::tmem_dealloc(tmem, nfi_mlp::kTmemCols);
+}
+
+}  // namespace nfi_ftc
 
 extern "C" int nfi_field_bwd(const NfiField* field, const float* planes_cl, const float* palette, int B,
                              int Hp, int Wp, const float* origins, const float* dirs, const float* z,
                              const float* points, int64_t n_per_image, int S, int mode, int img_w,
                              const float* g_out, float* g_planes_cl, float* g_palette, float* g_points,
                              float* g_params, nfi_stream_t stream) {
-  nfi_field::Args a;
+  using namespace nfi_ftc;
+  Args a;
   int rc = fill_args(a, "nfi_field_bwd", field, planes_cl, palette, B, Hp, Wp, origins, dirs, z, points,
                      n_per_image, S, mode, img_w);
   if (rc) return rc;
@@ -19,10 +266,26 @@ extern "C" int nfi_field_bwd(const NfiField* field, const float* planes_cl, cons
   NFI_REQUIRE(!g_planes_cl || nfi_aligned16(g_planes_cl), NFI_ERR_ALIGNMENT, "nfi_field_bwd: g_planes must be 16-byte aligned");
   a.g_out = g_out; a.g_planes = g_planes_cl; a.g_palette = (mode == 0) ? g_palette : nullptr;
   a.g_points = g_points; a.g_params = g_params;
-  const int grid = field_grid(a.n_tiles, 3);
+  const int grid = field_grid(a, 2);
+  const int smem = (int)sizeof(BwdSmem);
   cudaStream_t st = nfi_cu(stream);
-  if (mode == 0) nfi_field_bwd_launch_heads(a, grid, st);
-  else nfi_field_bwd_launch_raw(a, grid, st);
-  NFI_CHECK_LAUNCH("field_bwd_kernel");
+#define NFI_LAUNCH_BWD(P, M, W)                                                                         \
+  do {                                                                                                  \
+    cudaError_t e = cudaFuncSetAttribute(field_bwd_tc_kernel<P, M, W>,                                  \
+                                         cudaFuncAttributeMaxDynamicSharedMemorySize, smem);            \
+    NFI_REQUIRE(e == cudaSuccess, NFI_ERR_LAUNCH, "nfi_field_bwd: cudaFuncSetAttribute: %s",            \
+                cudaGetErrorString(e));                                                                 \
+    field_bwd_tc_kernel<P, M, W><<<grid, kThreads, smem, st>>>(a);                                      \
+  } while (0)
+  const bool wp = g_points != nullptr;
+  if (points) {
+    if (mode == 0) { if (wp) NFI_LAUNCH_BWD(true, 0, true); else NFI_LAUNCH_BWD(true, 0, false); }
+    else           { if (wp) NFI_LAUNCH_BWD(true, 1, true); else NFI_LAUNCH_BWD(true, 1, false); }
+  } else {
+    if (mode == 0) { if (wp) NFI_LAUNCH_BWD(false, 0, true); else NFI_LAUNCH_BWD(false, 0, false); }
+    else           { if (wp) NFI_LAUNCH_BWD(false, 1, true); else NFI_LAUNCH_BWD(false, 1, false); }
+  }
+#undef NFI_LAUNCH_BWD
+  NFI_CHECK_LAUNCH("field_bwd_tc_kernel");
   return NFI_OK;
 }

@@ -136,4 +136,109 @@ __device__ __forceinline__ void epilogue1(const Operands& s, uint32_t tmem_lane,
   for (int i = 0; i < 16; ++i) y[i] += s.b1[i];
 }
 
+// ---------------------------------------------------------------------------------------------
+// Backward (data gradients; the forward is recomputed per tile):
+//   dY[128 x 16] (hi, lo in TMEM)  ->  dH  [128 x 64] = dY . W1s          (B = W1s^T tile, K = 16)
+//   dHpre = dH * sigmoid(pre) (hi, lo in TMEM, over the H columns)
+//                                   ->  dF  [128 x 32] = dHpre . W0s       (B = W0s^T tile, K = 64)
+// TMEM columns: [0,64) D0 then dH | [64,192) H then dHpre (hi, lo) | [192,208) D1 | [208,240) dY (hi, lo)
+//               | dF reuses [192,224) once dH is complete
+// ---------------------------------------------------------------------------------------------
+constexpr int kColDH = 0, kColDYhi = 208, kColDYlo = 224, kColDF = 192;
+
+struct BwdWeights {
+  float w1t_hi[kH * kY], w1t_lo[kH * kY];   // [o/4][j][4]   element (n = j, k = o) = W1s[o][j]
+  float w0t_hi[kC * kH], w0t_lo[kC * kH];   // [j/4][k][4]   element (n = k, kk = j) = W0s[j][k]
+};
+
+__device__ __forceinline__ void load_weights_bwd(BwdWeights& s, const float* __restrict__ W0,
+                                                 const float* __restrict__ W1, int n_out) {
+  const float g0 = (float)(1.0 / sqrt((double)kC));
+  const float g1 = (float)(1.0 / sqrt((double)kH));
+  for (int i = threadIdx.x; i < kY * kH; i += blockDim.x) {
+    const int o = i / kH, j = i % kH;
+    const float w = o < n_out ? NFI_MUL(W1[i], g1) : 0.f;
+    const int d = (o >> 2) * (kLboW1t / 4) + j * 4 + (o & 3);
+    s.w1t_hi[d] = __uint_as_float(nfi_tc::tf32_hi(w));
+    s.w1t_lo[d] = nfi_tc::tf32_lo(w);
+  }
+  for (int i = threadIdx.x; i < kH * kC; i += blockDim.x) {
+    const int j = i / kC, k = i % kC;
+    const float w = NFI_MUL(W0[i], g0);
+    const int d = (j >> 2) * (kLboW0t / 4) + k * 4 + (j & 3);
+    s.w0t_hi[d] = __uint_as_float(nfi_tc::tf32_hi(w));
+    s.w0t_lo[d] = nfi_tc::tf32_lo(w);
+  }
+}
+
+// dH <- dY . W1s   (6 MMAs, K = 16) -- ONE thread
+__device__ __forceinline__ void issue_dh(const BwdWeights& s, uint32_t tmem) {
+  const uint32_t idesc = nfi_tc::idesc_tf32(kTile, kH);
+  const uint32_t b_hi = nfi_tc::smem_u32(s.w1t_hi), b_lo = nfi_tc::smem_u32(s.w1t_lo);
+  uint32_t acc = 0;
+#pragma unroll
+  for (int j = 0; j < kY / 8; ++j) {
+    const uint64_t bh = nfi_tc::smem_desc(b_hi + 2 * j * kLboW1t, kLboW1t, kSBO);
+    const uint64_t bl = nfi_tc::smem_desc(b_lo + 2 * j * kLboW1t, kLboW1t, kSBO);
+    nfi_tc::mma_tf32_ts(tmem + kColDH, tmem + kColDYlo + 8 * j, bh, idesc, acc); acc = 1;
+    nfi_tc::mma_tf32_ts(tmem + kColDH, tmem + kColDYhi + 8 * j, bl, idesc, 1);
+    nfi_tc::mma_tf32_ts(tmem + kColDH, tmem + kColDYhi + 8 * j, bh, idesc, 1);
+  }
+}
+
+// dF <- dHpre . W0s   (24 MMAs, K = 64) -- ONE thread
+__device__ __forceinline__ void issue_df(const BwdWeights& s, uint32_t tmem) {
+  const uint32_t idesc = nfi_tc::idesc_tf32(kTile, kC);
+  const uint32_t b_hi = nfi_tc::smem_u32(s.w0t_hi), b_lo = nfi_tc::smem_u32(s.w0t_lo);
+  uint32_t acc = 0;
+#pragma unroll
+  for (int j = 0; j < kH / 8; ++j) {
+    const uint64_t bh = nfi_tc::smem_desc(b_hi + 2 * j * kLboW0t, kLboW0t, kSBO);
+    const uint64_t bl = nfi_tc::smem_desc(b_lo + 2 * j * kLboW0t, kLboW0t, kSBO);
+    nfi_tc::mma_tf32_ts(tmem + kColDF, tmem + kColHlo + 8 * j, bh, idesc, acc); acc = 1;
+    nfi_tc::mma_tf32_ts(tmem + kColDF, tmem + kColHhi + 8 * j, bl, idesc, 1);
+    nfi_tc::mma_tf32_ts(tmem + kColDF, tmem + kColHhi + 8 * j, bh, idesc, 1);
+  }
+}
+
+// dY row (16 values, zero-padded) -> TMEM A operand (hi, lo)
+__device__ __forceinline__ void store_dy(uint32_t tmem_lane, const float (&dy)[16]) {
+  uint32_t hi[16], lo[16];
+#pragma unroll
+  for (int i = 0; i < 16; ++i) {
+    hi[i] = nfi_tc::tf32_hi(dy[i]);
+    lo[i] = __float_as_uint(dy[i] - __uint_as_float(hi[i]));
+  }
+  nfi_tc::tmem_st16(tmem_lane + kColDYhi, hi);
+  nfi_tc::tmem_st16(tmem_lane + kColDYlo, lo);
+  nfi_tc::tmem_st_wait();
+}
+
+// Epilogue 2 for 16*NQ hidden columns from col0: dHpre = dH * softplus'(pre), in place over H.
+// softplus'(pre) = sigmoid(pre) = 1 - exp(-h) with h = softplus(pre) = H_hi + H_lo (exactly the
+// value the forward used); for pre > 20 the reference's softplus is the identity (slope 1), and
+// 1 - exp(-h) rounds to 1 there.
+template <int NQ>
+__device__ __forceinline__ void epilogue2(uint32_t tmem_lane, int col0) {
+#pragma unroll
+  for (int q = 0; q < NQ; ++q) {
+    float dh[16], hh[16], hl[16];
+    nfi_tc::tmem_ld16(tmem_lane + kColDH + col0 + 16 * q, dh);
+    nfi_tc::tmem_ld16(tmem_lane + kColHhi + col0 + 16 * q, hh);
+    nfi_tc::tmem_ld16(tmem_lane + kColHlo + col0 + 16 * q, hl);
+    nfi_tc::tmem_ld_wait();
+    uint32_t hi[16], lo[16];
+#pragma unroll
+    for (int i = 0; i < 16; ++i) {
+      const float sg = 1.f - __expf(-(hh[i] + hl[i]));
+      const float g = dh[i] * sg;
+      hi[i] = nfi_tc::tf32_hi(g);
+      lo[i] = __float_as_uint(g - __uint_as_float(hi[i]));
+    }
+    nfi_tc::tmem_st16(tmem_lane + kColHhi + col0 + 16 * q, hi);
+    nfi_tc::tmem_st16(tmem_lane + kColHlo + col0 + 16 * q, lo);
+  }
+  nfi_tc::tmem_st_wait();
+}
+
 }  // namespace nfi_mlp
