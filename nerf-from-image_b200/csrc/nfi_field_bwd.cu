@@ -30,7 +30,7 @@ __device__ __forceinline__ void phase4_scatter(const Args& a, const Tables& t, c
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int c4 = lane & 7;
   const float third = 1.f / 3.f;
-  const int64_t plane_f4 = (int64_t)a.Hp * a.Wp * 8;
+  const int plane_f4 = a.Hp * a.Wp * 8;
 #pragma unroll 1
   for (int it = 0; it < 4; ++it) {
     const int s = warp * 16 + it * 4 + (lane >> 3);
@@ -43,7 +43,7 @@ __device__ __forceinline__ void phase4_scatter(const Args& a, const Tables& t, c
       for (int p = 0; p < 3; ++p) {
         const int4 o = t.toff[p][s];
         const float4 w = t.twgt[p][s];
-        const int64_t base = img_f4 + p * plane_f4;
+        const int64_t base = img_f4 + (int64_t)p * plane_f4;
         if (a.g_planes) {
           // a clamped neighbour (x1 == x0 at the border) carries weight 0: adding 0 is harmless
           float* G = a.g_planes;
@@ -75,7 +75,7 @@ __device__ __forceinline__ void phase4_scatter(const Args& a, const Tables& t, c
         gp[c] += __shfl_xor_sync(0xffffffffu, gp[c], 4);
       }
       if (c4 == 0 && t.keep[s] != -1.f) {
-        const int64_t id = sample_id(a, b, tt, s);
+        const int64_t id = (int64_t)b * (a.npi * a.S) + t.sid[s];
         const float inv_r = 1.f / a.f.scene_range;
         a.g_points[id * 3 + 0] = gp[0] * inv_r;
         a.g_points[id * 3 + 1] = gp[1] * inv_r;
@@ -109,6 +109,7 @@ field_bwd_tc_kernel(const Args a) {
   const bool want_pal = MODE == 0 && a.g_palette != nullptr;
   const bool want_par = MODE == 0 && a.g_params != nullptr && hd.use_sdf;
   uint32_t parity = 0;
+  const int64_t per_image = a.npi * a.S;
   for (int b = 0; b < a.B; ++b) {
     int64_t lo, hi;
     cta_tile_range(a.tiles_per_image, lo, hi);
@@ -124,8 +125,9 @@ field_bwd_tc_kernel(const Args a) {
 #pragma unroll
       for (int o = 0; o < NFI_YPAD; ++o) gy[o] = 0.f;
       if (tid < kTile) {
-        id = sample_id(a, b, tt, tid);
-        phase1<PTS, MODE, WANT_PTS>(a, t, id, b, tid);
+        const int sid = sample_in_image(a, (int)tt, tid);
+        if (sid >= 0) id = (int64_t)b * per_image + sid;
+        phase1<PTS, MODE, WANT_PTS>(a, t, id, sid, tid);
         if (id >= 0) {
           if (MODE == 0) {
             const float4 g = reinterpret_cast<const float4*>(a.g_out)[id];
@@ -146,7 +148,7 @@ field_bwd_tc_kernel(const Args a) {
       }
       const int any = __syncthreads_or(act ? 1 : 0);
       if (any) {
-        phase2_gather(a, t, op);
+        phase2_gather(a, t, op, b);
         nfi_tc::fence_proxy_async();
         nfi_tc::fence_before_sync();
         __syncthreads();

@@ -27,14 +27,16 @@ field_fwd_tc_kernel(const Args a) {
   const uint32_t tmem_lane = tmem + ((uint32_t)((warp & 3) * 32) << 16);
   const NfiHeads hd = make_heads(a.f);
   uint32_t parity = 0;
+  const int64_t per_image = a.npi * a.S;
   for (int b = 0; b < a.B; ++b) {
     int64_t lo, hi;
     cta_tile_range(a.tiles_per_image, lo, hi);
     for (int64_t tt = lo; tt < hi; ++tt) {
       int64_t id = -1;
       if (tid < kTile) {
-        id = sample_id(a, b, tt, tid);
-        phase1<PTS, MODE, false>(a, t, id, b, tid);
+        const int sid = sample_in_image(a, (int)tt, tid);
+        if (sid >= 0) id = (int64_t)b * per_image + sid;
+        phase1<PTS, MODE, false>(a, t, id, sid, tid);
       }
       const bool mine = tid < kTile && id >= 0 && sample_active(a, t.keep[tid]);
       const int any = __syncthreads_or(mine ? 1 : 0);
@@ -46,7 +48,7 @@ field_fwd_tc_kernel(const Args a) {
         __syncthreads();                           // tables are rewritten by the next tile
         continue;
       }
-      phase2_gather(a, t, op);
+      phase2_gather(a, t, op, b);
       nfi_tc::fence_proxy_async();
       nfi_tc::fence_before_sync();
       __syncthreads();

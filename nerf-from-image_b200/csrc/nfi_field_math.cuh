@@ -4,6 +4,14 @@
 #pragma once
 #include "nfi_math.cuh"
 
+// exp on the MUFU pipe in kernels (ex2.approx: relative error ~2^-21, far inside the 1e-4 contract);
+// the host emulation build (tests/hostcheck) uses libm.
+#if defined(__CUDA_ARCH__)
+#define NFI_EXPF(x) __expf(x)
+#else
+#define NFI_EXPF(x) expf(x)
+#endif
+
 // ---------------------------------------------------------------------------------------------
 // F.grid_sample(bilinear, border, align_corners=True), one axis   (ATen GridSampler.h)
 //   i = ((g + 1) / 2) * (size - 1); clamp to [0, size-1]; d i / d g = (size-1)/2 strictly inside
@@ -65,10 +73,10 @@ NFI_HD int nfi_plane_axis_b(int p) { return p == 0 ? 1 : 2; }
 //   W0jk [64][32]  (for the backward)
 //   W1jo [64][16]  (outputs padded to 16)
 // ---------------------------------------------------------------------------------------------
-NFI_HD float nfi_softplus(float x) { return x > 20.f ? x : log1pf(expf(x)); }
+NFI_HD float nfi_softplus(float x) { return x > 20.f ? x : log1pf(NFI_EXPF(x)); }
 NFI_HD float nfi_softplus_grad(float x) {
   if (x > 20.f) return 1.f;
-  const float e = expf(x);
+  const float e = NFI_EXPF(x);
   return e / (e + 1.f);
 }
 
@@ -171,7 +179,7 @@ NFI_HD void nfi_heads_fwd(const NfiHeads& hd, const float* y, float keep, const 
   const float dist = y[0];
   if (hd.use_sdf) {
     const float t = -dist;
-    const float e = expf(NFI_DIV(-fabsf(t), hd.beta));
+    const float e = NFI_EXPF(NFI_DIV(-fabsf(t), hd.beta));
     const float sgn = (t > 0.f) ? 1.f : ((t < 0.f) ? -1.f : 0.f);
     const float cdf = 0.5f + 0.5f * sgn * (1.f - e);
     sigma = hd.inv_alpha * (cdf * keep);
@@ -186,7 +194,7 @@ NFI_HD void nfi_heads_fwd(const NfiHeads& hd, const float* y, float keep, const 
     float s = 0.f;
 #pragma unroll
     for (int a = 0; a < NFI_YPAD - 1; ++a) {
-      probs[a] = (a < hd.A) ? expf(y[1 + a] - m) : 0.f;
+      probs[a] = (a < hd.A) ? NFI_EXPF(y[1 + a] - m) : 0.f;
       s += probs[a];
     }
     const float inv = 1.f / s;
@@ -201,7 +209,7 @@ NFI_HD void nfi_heads_fwd(const NfiHeads& hd, const float* y, float keep, const 
       }
     }
   } else {
-    for (int c = 0; c < 3; ++c) rgb[c] = (1.f / (1.f + expf(-y[1 + c]))) * 2.004f - 1.002f;
+    for (int c = 0; c < 3; ++c) rgb[c] = (1.f / (1.f + NFI_EXPF(-y[1 + c]))) * 2.004f - 1.002f;
   }
 }
 
@@ -216,7 +224,7 @@ NFI_HD void nfi_heads_bwd(const NfiHeads& hd, const float* y, float keep, const 
   if (hd.use_sdf) {
     const float t = -dist;
     const float at = fabsf(t);
-    const float e = expf(NFI_DIV(-at, hd.beta));
+    const float e = NFI_EXPF(NFI_DIV(-at, hd.beta));
     const float sgn = (t > 0.f) ? 1.f : ((t < 0.f) ? -1.f : 0.f);
     // d cdf / d t = 0.5 * sgn^2 * e / beta   (sign() has zero gradient, |t|' = sgn)
     const float dcdf_dt = 0.5f * sgn * sgn * e / hd.beta;

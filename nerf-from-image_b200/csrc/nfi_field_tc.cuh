@@ -43,18 +43,18 @@ struct Args {
   float* g_planes; float* g_palette; float* g_points; float* g_params;
 };
 
-// (image, tile-in-image, thread) -> linear sample id (ray * S + k), or -1
-__device__ __forceinline__ int64_t sample_id(const Args& a, int b, int64_t t, int tid) {
+// (tile-in-image, thread) -> sample index WITHIN the image (ray_in_image * S + k), or -1.
+// 32-bit arithmetic: fill_args guarantees npi * S < 2^31.
+__device__ __forceinline__ int sample_in_image(const Args& a, int t, int tid) {
   if (a.blocks_x == 0) {
-    const int64_t per_image = a.npi * a.S;
-    const int64_t local = t * kTile + tid;
-    return local < per_image ? (int64_t)b * per_image + local : -1;
+    const int64_t local = (int64_t)t * kTile + tid;
+    return local < a.npi * a.S ? (int)local : -1;
   }
-  const int64_t blk = t / a.S;                 // depth step fastest: consecutive tiles share texels
-  const int k = (int)(t - blk * a.S);
-  const int by = (int)(blk / a.blocks_x), bx = (int)(blk - (int64_t)by * a.blocks_x);
+  const int blk = t / a.S;                     // depth step fastest: consecutive tiles share texels
+  const int k = t - blk * a.S;
+  const int by = blk / a.blocks_x, bx = blk - by * a.blocks_x;
   const int py = tid >> 4, px = tid & 15;
-  const int64_t ray = (int64_t)b * a.npi + (int64_t)(by * 8 + py) * a.img_w + bx * 16 + px;
+  const int ray = (by * 8 + py) * a.img_w + bx * 16 + px;
   return ray * a.S + k;
 }
 
@@ -63,7 +63,7 @@ struct Tables {
   float4 twgt[3][kTile];    // ATen's weights nw, ne, sw, se
   float4 tder[3][kTile];    // backward only: (tx, ty, d ix / d x_a, d iy / d x_b) -- the last two are 0 where clamped
   float keep[kTile];        // 1 inside box, 0 outside, -1 no sample, -2 valid but nothing to do
-  int img[kTile];
+  int sid[kTile];           // sample index within the image (-1: none)
 };
 
 __device__ __forceinline__ bool sample_active(const Args& a, float keep) {
@@ -72,7 +72,7 @@ __device__ __forceinline__ bool sample_active(const Args& a, float keep) {
 
 // phase 1.  MODE 0: heads (out-of-box mask applies); MODE 1: raw decoder.  DER: fill tder.
 template <bool PTS, int MODE, bool DER>
-__device__ __forceinline__ void phase1(const Args& a, Tables& t, int64_t id, int b, int tid) {
+__device__ __forceinline__ void phase1(const Args& a, Tables& t, int64_t id, int sid, int tid) {
   float keep = -1.f;
   if (id >= 0) {
     float pt[3];
@@ -108,21 +108,21 @@ __device__ __forceinline__ void phase1(const Args& a, Tables& t, int64_t id, int
     }
   }
   t.keep[tid] = keep;
-  t.img[tid] = b;
+  t.sid[tid] = sid;
 }
 
 // phase 2: 256 threads gather 128 samples, 4 per warp pass, into the A-operand tile.
-__device__ __forceinline__ void phase2_gather(const Args& a, const Tables& t, nfi_mlp::Operands& op) {
+__device__ __forceinline__ void phase2_gather(const Args& a, const Tables& t, nfi_mlp::Operands& op, int b) {
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int c4 = lane & 7;
   const float third = 1.f / 3.f;
-  const int64_t plane_f4 = (int64_t)a.Hp * a.Wp * 8;
+  const int plane_f4 = a.Hp * a.Wp * 8;
+  const float4* base = reinterpret_cast<const float4*>(a.planes) + (int64_t)b * 3 * plane_f4 + c4;
 #pragma unroll 2
   for (int it = 0; it < 4; ++it) {
     const int s = warp * 16 + it * 4 + (lane >> 3);
     float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
     if (sample_active(a, t.keep[s])) {
-      const float4* base = reinterpret_cast<const float4*>(a.planes) + (int64_t)t.img[s] * 3 * plane_f4 + c4;
       float4 v[3][4];
       float4 w[3];
 #pragma unroll

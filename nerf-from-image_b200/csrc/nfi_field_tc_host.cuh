@@ -24,6 +24,7 @@ static inline int fill_args(Args& a, const char* who, const NfiField* field, con
   NFI_REQUIRE(nfi_aligned16(planes_cl), NFI_ERR_ALIGNMENT, "%s: planes must be 16-byte aligned", who);
   NFI_REQUIRE(B > 0 && Hp >= 2 && Wp >= 2 && n_per_image > 0 && S >= 1, NFI_ERR_BAD_ARG, "%s: bad sizes", who);
   NFI_REQUIRE((int64_t)Hp * Wp * 8 < (int64_t)1 << 31, NFI_ERR_UNSUPPORTED, "%s: plane too large", who);
+  NFI_REQUIRE(n_per_image * S < ((int64_t)1 << 31) - kTile, NFI_ERR_UNSUPPORTED, "%s: more than 2^31 samples per image", who);
   NFI_REQUIRE(mode == 0 || mode == 1, NFI_ERR_BAD_ARG, "%s: mode must be 0 or 1", who);
   NFI_REQUIRE(points || (origins && dirs && z), NFI_ERR_BAD_ARG, "%s: need points or origins/dirs/z", who);
   NFI_REQUIRE(!points || S == 1, NFI_ERR_BAD_ARG, "%s: explicit points need S = 1", who);

@@ -101,8 +101,13 @@ __device__ __forceinline__ void issue_layer1(const Operands& s, uint32_t tmem) {
   }
 }
 
-// softplus with the reference's threshold (torch.nn.Softplus: beta = 1, threshold = 20)
-__device__ __forceinline__ float softplus_f(float x) { return x > 20.f ? x : log1pf(expf(x)); }
+// softplus (torch.nn.Softplus: beta = 1, threshold = 20) as max(x, 0) + log(1 + exp(-|x|)) on the
+// MUFU pipe (ex2.approx / lg2.approx): absolute error < 3e-7, and for x > 20 the correction term
+// is below 2.1e-9, i.e. the reference's linear branch within fp32 resolution.
+__device__ __forceinline__ float softplus_f(float x) {
+  const float t = __expf(-fabsf(x));
+  return fmaxf(x, 0.f) + __logf(1.f + t);
+}
 
 // Epilogue 0 for 16*NQ hidden columns starting at col0 of this thread's TMEM lane:
 // D0 -> H = softplus(D0 + b0) -> TMEM (hi, lo).  hpre (optional) keeps the pre-activations.
