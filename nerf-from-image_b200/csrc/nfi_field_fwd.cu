@@ -1,4 +1,7 @@
 // Forward of the fused triplane field (gather + tcgen05 MLP + heads), see nfi_field_tc.cuh.
+#include <stdlib.h>
+
+#include "nfi_field_fwd_ws.cuh"
 #include "nfi_field_tc_host.cuh"
 
 namespace nfi_ftc {
@@ -170,9 +173,25 @@ extern "C" int nfi_field_fwd(const NfiField* field, const float* planes_cl, cons
   NFI_REQUIRE(out, NFI_ERR_BAD_ARG, "nfi_field_fwd: NULL output");
   NFI_REQUIRE(mode == 1 || nfi_aligned16(out), NFI_ERR_ALIGNMENT, "nfi_field_fwd: out must be 16-byte aligned");
   a.out = out; a.probs = probs_out; a.skip_oob = skip_oob;
+  cudaStream_t st = nfi_cu(stream);
+  static const bool simple = getenv("NFI_FWD_SIMPLE") != nullptr;     // development A/B switch
+  if (!simple) {
+    const int grid = field_grid(a, 1);
+    const int smem = (int)sizeof(WsFwdSmem);
+#define NFI_LAUNCH_WS(P, M)                                                               \
+  do {                                                                                    \
+    rc = set_smem(field_fwd_ws_kernel<P, M>, smem, "nfi_field_fwd");                      \
+    if (rc) return rc;                                                                    \
+    field_fwd_ws_kernel<P, M><<<grid, kWsThreads, smem, st>>>(a);                         \
+  } while (0)
+    if (points) { if (mode == 0) NFI_LAUNCH_WS(true, 0); else NFI_LAUNCH_WS(true, 1); }
+    else        { if (mode == 0) NFI_LAUNCH_WS(false, 0); else NFI_LAUNCH_WS(false, 1); }
+#undef NFI_LAUNCH_WS
+    NFI_CHECK_LAUNCH("field_fwd_ws_kernel");
+    return NFI_OK;
+  }
   const int grid = field_grid(a, 2);
   const int smem = (int)sizeof(FwdSmem);
-  cudaStream_t st = nfi_cu(stream);
 #define NFI_LAUNCH_FWD(P, M)                                                              \
   do {                                                                                    \
     rc = set_smem(field_fwd_tc_kernel<P, M>, smem, "nfi_field_fwd");                      \

@@ -179,7 +179,7 @@ NFI_HD void nfi_heads_fwd(const NfiHeads& hd, const float* y, float keep, const 
   const float dist = y[0];
   if (hd.use_sdf) {
     const float t = -dist;
-    const float e = NFI_EXPF(NFI_DIV(-fabsf(t), hd.beta));
+    const float e = expf(NFI_DIV(-fabsf(t), hd.beta));   // full precision: sigma feeds exp(-sigma * dist)
     const float sgn = (t > 0.f) ? 1.f : ((t < 0.f) ? -1.f : 0.f);
     const float cdf = 0.5f + 0.5f * sgn * (1.f - e);
     sigma = hd.inv_alpha * (cdf * keep);
@@ -224,7 +224,7 @@ NFI_HD void nfi_heads_bwd(const NfiHeads& hd, const float* y, float keep, const 
   if (hd.use_sdf) {
     const float t = -dist;
     const float at = fabsf(t);
-    const float e = NFI_EXPF(NFI_DIV(-at, hd.beta));
+    const float e = expf(NFI_DIV(-at, hd.beta));
     const float sgn = (t > 0.f) ? 1.f : ((t < 0.f) ? -1.f : 0.f);
     // d cdf / d t = 0.5 * sgn^2 * e / beta   (sign() has zero gradient, |t|' = sgn)
     const float dcdf_dt = 0.5f * sgn * sgn * e / hd.beta;

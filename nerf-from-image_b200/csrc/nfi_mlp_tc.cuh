@@ -142,6 +142,108 @@ __device__ __forceinline__ void epilogue1(const Operands& s, uint32_t tmem_lane,
 }
 
 // ---------------------------------------------------------------------------------------------
+// Explicit-address variants for the warp-specialised (pipelined) kernels: several feature-tile
+// stages in shared memory and two accumulator sets in TMEM.
+// ---------------------------------------------------------------------------------------------
+struct FwdWeights {
+  float w0_hi[kH * kC], w0_lo[kH * kC];  // [k/4][n][4]
+  float w1_hi[kY * kH], w1_lo[kY * kH];  // [k/4][n][4]
+  float b0[kH];
+  float b1[kY];
+};
+constexpr int kStageFloats = 8 * kLboA / 4;      // one hi (or lo) feature tile
+
+__device__ __forceinline__ void load_weights(FwdWeights& s, const float* __restrict__ W0,
+                                             const float* __restrict__ b0, const float* __restrict__ W1,
+                                             const float* __restrict__ b1, int n_out) {
+  const float g0 = (float)(1.0 / sqrt((double)kC));
+  const float g1 = (float)(1.0 / sqrt((double)kH));
+  for (int i = threadIdx.x; i < kH * kC; i += blockDim.x) {
+    const int n = i / kC, k = i % kC;
+    const float w = NFI_MUL(W0[i], g0);
+    const int o = (k >> 2) * (kLboW0 / 4) + n * 4 + (k & 3);
+    s.w0_hi[o] = __uint_as_float(nfi_tc::tf32_hi(w));
+    s.w0_lo[o] = nfi_tc::tf32_lo(w);
+  }
+  for (int i = threadIdx.x; i < kY * kH; i += blockDim.x) {
+    const int n = i / kH, k = i % kH;
+    const float w = n < n_out ? NFI_MUL(W1[i], g1) : 0.f;
+    const int o = (k >> 2) * (kLboW1 / 4) + n * 4 + (k & 3);
+    s.w1_hi[o] = __uint_as_float(nfi_tc::tf32_hi(w));
+    s.w1_lo[o] = nfi_tc::tf32_lo(w);
+  }
+  for (int i = threadIdx.x; i < kH; i += blockDim.x) s.b0[i] = b0[i];
+  for (int i = threadIdx.x; i < kY; i += blockDim.x) s.b1[i] = i < n_out ? b1[i] : 0.f;
+}
+
+// feature row chunk -> stage tile (a_hi, a_lo point at the stage's two tiles)
+__device__ __forceinline__ void store_feat4(float* a_hi, float* a_lo, int row, int c4, float4 v) {
+  const int o = c4 * (kLboA / 4) + row * 4;
+  const uint32_t hx = nfi_tc::tf32_hi(v.x), hy = nfi_tc::tf32_hi(v.y), hz = nfi_tc::tf32_hi(v.z), hw = nfi_tc::tf32_hi(v.w);
+  *reinterpret_cast<float4*>(a_hi + o) = make_float4(__uint_as_float(hx), __uint_as_float(hy), __uint_as_float(hz), __uint_as_float(hw));
+  *reinterpret_cast<float4*>(a_lo + o) = make_float4(v.x - __uint_as_float(hx), v.y - __uint_as_float(hy),
+                                                     v.z - __uint_as_float(hz), v.w - __uint_as_float(hw));
+}
+
+// tacc = TMEM address of the accumulator set (column base of its D0)
+__device__ __forceinline__ void issue_layer0_at(const FwdWeights& w, const float* a_hi_p, const float* a_lo_p,
+                                                uint32_t tacc) {
+  const uint32_t idesc = nfi_tc::idesc_tf32(kTile, kH);
+  const uint32_t a_hi = nfi_tc::smem_u32(a_hi_p), a_lo = nfi_tc::smem_u32(a_lo_p);
+  const uint32_t b_hi = nfi_tc::smem_u32(w.w0_hi), b_lo = nfi_tc::smem_u32(w.w0_lo);
+  uint32_t acc = 0;
+#pragma unroll
+  for (int j = 0; j < kC / 8; ++j) {
+    const uint64_t ah = nfi_tc::smem_desc(a_hi + 2 * j * kLboA, kLboA, kSBO);
+    const uint64_t al = nfi_tc::smem_desc(a_lo + 2 * j * kLboA, kLboA, kSBO);
+    const uint64_t bh = nfi_tc::smem_desc(b_hi + 2 * j * kLboW0, kLboW0, kSBO);
+    const uint64_t bl = nfi_tc::smem_desc(b_lo + 2 * j * kLboW0, kLboW0, kSBO);
+    nfi_tc::mma_tf32_ss(tacc + kColD0, al, bh, idesc, acc); acc = 1;
+    nfi_tc::mma_tf32_ss(tacc + kColD0, ah, bl, idesc, 1);
+    nfi_tc::mma_tf32_ss(tacc + kColD0, ah, bh, idesc, 1);
+  }
+}
+__device__ __forceinline__ void issue_layer1_at(const FwdWeights& w, uint32_t tacc) {
+  const uint32_t idesc = nfi_tc::idesc_tf32(kTile, kY);
+  const uint32_t b_hi = nfi_tc::smem_u32(w.w1_hi), b_lo = nfi_tc::smem_u32(w.w1_lo);
+  uint32_t acc = 0;
+#pragma unroll
+  for (int j = 0; j < kH / 8; ++j) {
+    const uint64_t bh = nfi_tc::smem_desc(b_hi + 2 * j * kLboW1, kLboW1, kSBO);
+    const uint64_t bl = nfi_tc::smem_desc(b_lo + 2 * j * kLboW1, kLboW1, kSBO);
+    nfi_tc::mma_tf32_ts(tacc + kColD1, tacc + kColHlo + 8 * j, bh, idesc, acc); acc = 1;
+    nfi_tc::mma_tf32_ts(tacc + kColD1, tacc + kColHhi + 8 * j, bl, idesc, 1);
+    nfi_tc::mma_tf32_ts(tacc + kColD1, tacc + kColHhi + 8 * j, bh, idesc, 1);
+  }
+}
+// epilogue 0 on accumulator set tl (= tacc + lane offset of this warp)
+template <int NQ>
+__device__ __forceinline__ void epilogue0_at(const float* __restrict__ b0, uint32_t tl, int col0) {
+#pragma unroll
+  for (int q = 0; q < NQ; ++q) {
+    float v[16];
+    nfi_tc::tmem_ld16(tl + kColD0 + col0 + 16 * q, v);
+    nfi_tc::tmem_ld_wait();
+    uint32_t hi[16], lo[16];
+#pragma unroll
+    for (int i = 0; i < 16; ++i) {
+      const float h = softplus_f(v[i] + b0[col0 + 16 * q + i]);
+      hi[i] = nfi_tc::tf32_hi(h);
+      lo[i] = __float_as_uint(h - __uint_as_float(hi[i]));
+    }
+    nfi_tc::tmem_st16(tl + kColHhi + col0 + 16 * q, hi);
+    nfi_tc::tmem_st16(tl + kColHlo + col0 + 16 * q, lo);
+  }
+  nfi_tc::tmem_st_wait();
+}
+__device__ __forceinline__ void epilogue1_at(const float* __restrict__ b1, uint32_t tl, float (&y)[16]) {
+  nfi_tc::tmem_ld16(tl + kColD1, y);
+  nfi_tc::tmem_ld_wait();
+#pragma unroll
+  for (int i = 0; i < 16; ++i) y[i] += b1[i];
+}
+
+// ---------------------------------------------------------------------------------------------
 // Backward (data gradients; the forward is recomputed per tile):
 //   dY[128 x 16] (hi, lo in TMEM)  ->  dH  [128 x 64] = dY . W1s          (B = W1s^T tile, K = 16)
 //   dHpre = dH * sigmoid(pre) (hi, lo in TMEM, over the H columns)

@@ -79,8 +79,30 @@ __device__ __forceinline__ uint32_t mbar_try_wait(uint64_t* bar, uint32_t parity
       : "=r"(ok) : "r"(smem_u32(bar)), "r"(parity) : "memory");
   return ok;
 }
+// Bounded wait: a protocol bug must surface as a launch error (trap), never as a hung GPU.
 __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
-  while (!mbar_try_wait(bar, parity)) {}
+  uint32_t spins = 0;
+  while (!mbar_try_wait(bar, parity)) {
+    if (++spins > (1u << 24)) __trap();
+  }
+}
+// thread arrival (release.cta): the arriving thread's earlier shared-memory writes are visible to
+// a thread that observes the phase completion
+__device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
+  asm volatile("{\n\t.reg .b64 st;\n\tmbarrier.arrive.shared::cta.b64 st, [%0];\n\t}\n" :: "r"(smem_u32(bar)) : "memory");
+}
+// named barrier over `nthreads` threads (ids 1..15; 0 is __syncthreads), with an OR reduction
+__device__ __forceinline__ uint32_t named_bar_or(uint32_t id, uint32_t nthreads, uint32_t pred) {
+  uint32_t out;
+  asm volatile(
+      "{\n\t.reg .pred p, q;\n\tsetp.ne.u32 q, %3, 0;\n\t"
+      "bar.red.or.pred p, %1, %2, q;\n\t"
+      "selp.u32 %0, 1, 0, p;\n\t}\n"
+      : "=r"(out) : "r"(id), "r"(nthreads), "r"(pred) : "memory");
+  return out;
+}
+__device__ __forceinline__ void named_bar_sync(uint32_t id, uint32_t nthreads) {
+  asm volatile("bar.sync %0, %1;" :: "r"(id), "r"(nthreads) : "memory");
 }
 
 // ---- TMEM allocation (one full warp) ------------------------------------------------------------
