@@ -89,7 +89,10 @@ int nfi_points_bwd(const float* g_points, const float* z, int64_t R, int S, floa
                    float* g_dirs, nfi_stream_t stream);
 
 /* ---- layout boundary: StyleGAN2 planes [B, 3*32, Hp, Wp] NCHW (models/generator.py:475-477)
- *      <-> channels-last [B, 3, Hp, Wp, 32] used by the gather/scatter kernels --------------------- */
+ *      <-> channels-last [B, 3, Hp*Wp, 32] used by the gather/scatter kernels.  The texel order
+ *      inside a plane is the library's own (8 x 8 texel blocks when Hp and Wp are multiples of 8,
+ *      else row-major): `planes_cl` buffers are opaque -- only these two calls produce / consume
+ *      them, and every `planes_cl` / `g_planes_cl` argument below expects this layout. -------------- */
 int nfi_planes_to_cl(const float* planes_nchw, int B, int Hp, int Wp, float* planes_cl,
                      nfi_stream_t stream);
 int nfi_planes_grad_from_cl(const float* g_planes_cl, int B, int Hp, int Wp, float* g_planes_nchw,

@@ -14,7 +14,8 @@ from ctypes import POINTER, Structure, c_char_p, c_float, c_int, c_int32, c_int6
 import torch
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(HERE, "lib", "libnfi_b200.so")
+# NFI_B200_LIB: developer switch to load another build of the same library (kernel A/B runs)
+LIB_PATH = os.environ.get("NFI_B200_LIB") or os.path.join(HERE, "lib", "libnfi_b200.so")
 
 
 class NfiError(RuntimeError):

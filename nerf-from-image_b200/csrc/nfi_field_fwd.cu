@@ -1,118 +1,23 @@
 // Forward of the fused triplane field (gather + tcgen05 MLP + heads), see nfi_field_tc.cuh.
+#include <stdio.h>
 #include <stdlib.h>
 
 #include "nfi_field_fwd_ws.cuh"
 #include "nfi_field_tc_host.cuh"
 
-namespace nfi_ftc {
-
-struct FwdSmem {
-  nfi_mlp::Operands op;
-  Tables t;
-};
-
-template <bool PTS, int MODE>
-__global__ void __launch_bounds__(kThreads, 2)
-field_fwd_tc_kernel(const Args a) {
-  extern __shared__ __align__(128) unsigned char smem_raw[];
-  FwdSmem& sm = *reinterpret_cast<FwdSmem*>(smem_raw);
-  nfi_mlp::Operands& op = sm.op;
-  Tables& t = sm.t;
-  const int tid = threadIdx.x, warp = tid >> 5;
-  nfi_mlp::load_weights(op, a.f.W0, a.f.b0, a.f.W1, a.f.b1, a.f.n_out);
-  if (warp == 0) nfi_tc::tmem_alloc(&op.tmem_base, nfi_mlp::kTmemCols);
-  if (tid == 0) { nfi_tc::mbar_init(&op.bar, 1); nfi_tc::mbar_fence_init(); }
-  nfi_tc::fence_proxy_async();
-  nfi_tc::fence_before_sync();
-  __syncthreads();
-  nfi_tc::fence_after_sync();
-  const uint32_t tmem = op.tmem_base;
-  const uint32_t tmem_lane = tmem + ((uint32_t)((warp & 3) * 32) << 16);
-  const NfiHeads hd = make_heads(a.f);
-  uint32_t parity = 0;
-  const int64_t per_image = a.npi * a.S;
-  for (int b = 0; b < a.B; ++b) {
-    int64_t lo, hi;
-    cta_tile_range(a.tiles_per_image, lo, hi);
-    for (int64_t tt = lo; tt < hi; ++tt) {
-      int64_t id = -1;
-      if (tid < kTile) {
-        const int sid = sample_in_image(a, (int)tt, tid);
-        if (sid >= 0) id = (int64_t)b * per_image + sid;
-        phase1<PTS, MODE, false>(a, t, id, sid, tid);
-      }
-      const bool mine = tid < kTile && id >= 0 && sample_active(a, t.keep[tid]);
-      const int any = __syncthreads_or(mine ? 1 : 0);
-      if (!any) {                                  // whole tile outside the box: zeros, no gather, no MMA
-        if (MODE == 0 && id >= 0) {
-          reinterpret_cast<float4*>(a.out)[id] = make_float4(0.f, 0.f, 0.f, 0.f);
-          if (a.probs) for (int q = 0; q < hd.A; ++q) a.probs[id * hd.A + q] = 0.f;
-        }
-        __syncthreads();                           // tables are rewritten by the next tile
-        continue;
-      }
-      phase2_gather(a, t, op, b);
-      nfi_tc::fence_proxy_async();
-      nfi_tc::fence_before_sync();
-      __syncthreads();
-      if (tid == 0) {
-        nfi_tc::fence_after_sync();
-        nfi_mlp::issue_layer0(op, tmem);
-        nfi_tc::mma_commit(&op.bar);
-      }
-      nfi_tc::mbar_wait(&op.bar, parity); parity ^= 1;
-      nfi_tc::fence_after_sync();
-      nfi_mlp::epilogue0<2, false>(op, tmem_lane, (warp >> 2) * 32, nullptr);
-      nfi_tc::fence_before_sync();
-      __syncthreads();
-      if (tid == 0) {
-        nfi_tc::fence_after_sync();
-        nfi_mlp::issue_layer1(op, tmem);
-        nfi_tc::mma_commit(&op.bar);
-      }
-      if (warp < 4) {
-        nfi_tc::mbar_wait(&op.bar, parity);
-        nfi_tc::fence_after_sync();
-        float y[nfi_mlp::kY];
-        nfi_mlp::epilogue1(op, tmem_lane, y);
-        if (id >= 0) {
-          const float keep = t.keep[tid];
-          if (MODE == 0) {
-            if (!sample_active(a, keep)) {
-              reinterpret_cast<float4*>(a.out)[id] = make_float4(0.f, 0.f, 0.f, 0.f);
-              if (a.probs) for (int q = 0; q < hd.A; ++q) a.probs[id * hd.A + q] = 0.f;
-            } else {
-              float sigma, rgb[3], probs[NFI_YPAD - 1];
-              nfi_heads_fwd(hd, y, keep, a.palette ? a.palette + (int64_t)b * hd.A * 3 : nullptr, sigma, rgb, probs);
-              reinterpret_cast<float4*>(a.out)[id] = make_float4(sigma, rgb[0], rgb[1], rgb[2]);
-              if (a.probs) {
-#pragma unroll
-                for (int q = 0; q < NFI_YPAD - 1; ++q) if (q < hd.A) a.probs[id * hd.A + q] = probs[q];
-              }
-            }
-          } else {
-#pragma unroll
-            for (int o = 0; o < NFI_YPAD; ++o) if (o < a.f.n_out) a.out[id * a.f.n_out + o] = y[o];
-          }
-        }
-        nfi_tc::fence_before_sync();
-      }
-      parity ^= 1;
-    }
-  }
-  __syncthreads();
-  if (warp == 0) nfi_tc::tmem_dealloc(tmem, nfi_mlp::kTmemCols);
-}
-
-}  // namespace nfi_ftc
-
 namespace {
 
-// [B*3][32][HW] -> [B*3][HW][32] (and back).  32 x 32 tiles through padded shared memory: both the
-// global reads and the global writes are 128-byte coalesced.
+// [B*3][32][HW] -> [B*3][HW][32] (and back), the channels-last side in the texel order of
+// nfi_field_math.cuh.  32 x 32 tiles through padded shared memory: the NCHW side is 128-byte coalesced,
+// the channels-last side moves whole 128-byte texels.
+__device__ __forceinline__ int texel_index(int p, int Wp, int bshift) {
+  const int y = p / Wp, x = p - y * Wp;
+  return nfi_texel_row(y, bshift, Wp >> bshift) + nfi_texel_col(x, bshift);
+}
+
 template <bool TO_CL>
 __global__ void __launch_bounds__(256)
-plane_transpose_kernel(const float* __restrict__ src, float* __restrict__ dst, int HW) {
+plane_transpose_kernel(const float* __restrict__ src, float* __restrict__ dst, int HW, int Wp, int bshift) {
   __shared__ float tile[32][33];
   const int64_t plane = blockIdx.y;
   const int p0 = blockIdx.x * 32;
@@ -124,10 +29,10 @@ plane_transpose_kernel(const float* __restrict__ src, float* __restrict__ dst, i
     for (int c = ty; c < 32; c += 8) tile[c][tx] = (p0 + tx < HW) ? s[(int64_t)c * HW + p0 + tx] : 0.f;
     __syncthreads();
 #pragma unroll
-    for (int p = ty; p < 32; p += 8) if (p0 + p < HW) d[(int64_t)(p0 + p) * 32 + tx] = tile[tx][p];
+    for (int p = ty; p < 32; p += 8) if (p0 + p < HW) d[(int64_t)texel_index(p0 + p, Wp, bshift) * 32 + tx] = tile[tx][p];
   } else {
 #pragma unroll
-    for (int p = ty; p < 32; p += 8) tile[p][tx] = (p0 + p < HW) ? s[(int64_t)(p0 + p) * 32 + tx] : 0.f;
+    for (int p = ty; p < 32; p += 8) tile[p][tx] = (p0 + p < HW) ? s[(int64_t)texel_index(p0 + p, Wp, bshift) * 32 + tx] : 0.f;
     __syncthreads();
 #pragma unroll
     for (int c = ty; c < 32; c += 8) if (p0 + tx < HW) d[(int64_t)c * HW + p0 + tx] = tile[tx][c];
@@ -147,7 +52,7 @@ extern "C" int nfi_planes_to_cl(const float* planes_nchw, int B, int Hp, int Wp,
                                 nfi_stream_t stream) {
   NFI_REQUIRE(planes_nchw && planes_cl && B > 0 && Hp > 0 && Wp > 0, NFI_ERR_BAD_ARG, "nfi_planes_to_cl: bad argument");
   const int HW = Hp * Wp;
-  plane_transpose_kernel<true><<<dim3((HW + 31) / 32, B * 3), 256, 0, nfi_cu(stream)>>>(planes_nchw, planes_cl, HW);
+  plane_transpose_kernel<true><<<dim3((HW + 31) / 32, B * 3), 256, 0, nfi_cu(stream)>>>(planes_nchw, planes_cl, HW, Wp, nfi_plane_bshift(Hp, Wp));
   NFI_CHECK_LAUNCH("plane_transpose_kernel<to_cl>");
   return NFI_OK;
 }
@@ -156,7 +61,7 @@ extern "C" int nfi_planes_grad_from_cl(const float* g_planes_cl, int B, int Hp, 
                                        float* g_planes_nchw, nfi_stream_t stream) {
   NFI_REQUIRE(g_planes_cl && g_planes_nchw && B > 0 && Hp > 0 && Wp > 0, NFI_ERR_BAD_ARG, "nfi_planes_grad_from_cl: bad argument");
   const int HW = Hp * Wp;
-  plane_transpose_kernel<false><<<dim3((HW + 31) / 32, B * 3), 256, 0, nfi_cu(stream)>>>(g_planes_cl, g_planes_nchw, HW);
+  plane_transpose_kernel<false><<<dim3((HW + 31) / 32, B * 3), 256, 0, nfi_cu(stream)>>>(g_planes_cl, g_planes_nchw, HW, Wp, nfi_plane_bshift(Hp, Wp));
   NFI_CHECK_LAUNCH("plane_transpose_kernel<from_cl>");
   return NFI_OK;
 }
@@ -174,8 +79,7 @@ extern "C" int nfi_field_fwd(const NfiField* field, const float* planes_cl, cons
   NFI_REQUIRE(mode == 1 || nfi_aligned16(out), NFI_ERR_ALIGNMENT, "nfi_field_fwd: out must be 16-byte aligned");
   a.out = out; a.probs = probs_out; a.skip_oob = skip_oob;
   cudaStream_t st = nfi_cu(stream);
-  static const bool simple = getenv("NFI_FWD_SIMPLE") != nullptr;     // development A/B switch
-  if (!simple) {
+  {
     const int grid = field_grid(a, 1);
     const int smem = (int)sizeof(WsFwdSmem);
 #define NFI_LAUNCH_WS(P, M)                                                               \
@@ -188,19 +92,25 @@ extern "C" int nfi_field_fwd(const NfiField* field, const float* planes_cl, cons
     else        { if (mode == 0) NFI_LAUNCH_WS(false, 0); else NFI_LAUNCH_WS(false, 1); }
 #undef NFI_LAUNCH_WS
     NFI_CHECK_LAUNCH("field_fwd_ws_kernel");
+#ifdef NFI_WS_TRACE
+    if (const char* path = getenv("NFI_WS_TRACE_FILE")) {       // developer builds only: blocking dump
+      static int launch = 0;
+      static long long host[kTrRoles * kTrN * kTrEv];
+      cudaStreamSynchronize(st);
+      cudaMemcpyFromSymbol(host, g_ws_trace, sizeof(host));
+      char name[512];
+      snprintf(name, sizeof(name), "%s.%d", path, launch++ % 2);
+      if (FILE* fp = fopen(name, "w")) {
+        for (int r = 0; r < kTrRoles; ++r)
+          for (int t = 0; t < kTrN; ++t) {
+            fprintf(fp, "%d %d", r, t);
+            for (int e = 0; e < kTrEv; ++e) fprintf(fp, " %lld", host[(r * kTrN + t) * kTrEv + e]);
+            fprintf(fp, "\n");
+          }
+        fclose(fp);
+      }
+    }
+#endif
     return NFI_OK;
   }
-  const int grid = field_grid(a, 2);
-  const int smem = (int)sizeof(FwdSmem);
-#define NFI_LAUNCH_FWD(P, M)                                                              \
-  do {                                                                                    \
-    rc = set_smem(field_fwd_tc_kernel<P, M>, smem, "nfi_field_fwd");                      \
-    if (rc) return rc;                                                                    \
-    field_fwd_tc_kernel<P, M><<<grid, kThreads, smem, st>>>(a);                           \
-  } while (0)
-  if (points) { if (mode == 0) NFI_LAUNCH_FWD(true, 0); else NFI_LAUNCH_FWD(true, 1); }
-  else        { if (mode == 0) NFI_LAUNCH_FWD(false, 0); else NFI_LAUNCH_FWD(false, 1); }
-#undef NFI_LAUNCH_FWD
-  NFI_CHECK_LAUNCH("field_fwd_tc_kernel");
-  return NFI_OK;
 }

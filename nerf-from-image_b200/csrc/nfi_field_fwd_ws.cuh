@@ -1,8 +1,8 @@
 // Warp-specialised, software-pipelined forward of the fused triplane field (one persistent CTA per
-// SM, 17 warps).  Roles talk through mbarriers only; no __syncthreads inside the tile loop.
+// SM, 25 warps).  Roles talk through mbarriers only; no __syncthreads inside the tile loop.
 //
-//   producers  (8 warps)  phase 1 (coords -> texel offsets / weights) + phase 2 (gather) of tile i+1
-//                         into a 2-stage ring of UMMA A-operand tiles, while ...
+//   producers  (2 x 8 warps) phase 1 (coords -> texel offsets / weights) + phase 2 (gather) of tiles
+//                         i+1, i+2 (one per group) into a ring of UMMA A-operand tiles, while ...
 //   MMA thread (1 warp)   ... issues tcgen05.mma for whichever tile has its operands ready
 //                         (layer 0 of tile i+1 goes ahead of layer 1 of tile i), and ...
 //   epilogue   (8 warps)  ... runs softplus / hi-lo split / heads of tile i out of TMEM
@@ -21,31 +21,60 @@
 
 namespace nfi_ftc {
 
-constexpr int kWsProducerWarps = 8, kWsEpilogueWarps = 8;
-constexpr int kWsThreads = (kWsProducerWarps + kWsEpilogueWarps + 1) * 32;   // 544
-constexpr int kNS = 3;      // operand stages
-constexpr int kNM = 4;      // meta stages
+#ifndef NFI_WS_GROUPS
+#define NFI_WS_GROUPS 2
+#endif
+#ifndef NFI_WS_GROUP_WARPS
+#define NFI_WS_GROUP_WARPS 4
+#endif
+constexpr int kWsGroups = NFI_WS_GROUPS;          // producer groups: group g prepares tiles it % kWsGroups == g
+constexpr int kWsGroupWarps = NFI_WS_GROUP_WARPS; // warps per group
+constexpr int kWsRows = kTile / kWsGroupWarps;    // rows of the tile owned by one producer warp (16 or 32)
+constexpr int kWsProducerWarps = kWsGroups * kWsGroupWarps, kWsEpilogueWarps = 8;
+constexpr int kWsThreads = (kWsProducerWarps + kWsEpilogueWarps + 1) * 32;   // 800
+#ifndef NFI_WS_STAGES
+#define NFI_WS_STAGES 3
+#endif
+constexpr int kNS = NFI_WS_STAGES;      // operand stages
+constexpr int kNM = 8;      // meta stages (a producer is never more than kNM tiles ahead of the heads)
 constexpr int kNA = 2;      // accumulator sets
 constexpr int kAccCols = 256;
+
+// Developer trace (-DNFI_WS_TRACE builds only): SM clock at pipeline events of CTA 0, tiles
+// [kTrT0, kTrT0 + kTrN) of the launch; dumped by the host after the launch (NFI_WS_TRACE_FILE).
+#ifdef NFI_WS_TRACE
+constexpr int kTrRoles = 5, kTrN = 128, kTrEv = 4, kTrT0 = 256;
+__device__ long long g_ws_trace[kTrRoles * kTrN * kTrEv];
+#define NFI_TRACE(role, it, ev)                                                                     \
+  do {                                                                                              \
+    if (blockIdx.x == 0 && (it) >= (uint32_t)kTrT0 && (it) < (uint32_t)(kTrT0 + kTrN))              \
+      g_ws_trace[((role) * kTrN + ((it) - kTrT0)) * kTrEv + (ev)] = clock64();                      \
+  } while (0)
+#else
+#define NFI_TRACE(role, it, ev) do {} while (0)
+#endif
 
 struct WsMeta {
   float keep[kTile];
   int sid[kTile];
-  int flag[8];      // per producer warp: any of its 16 samples active
+  int flag[kWsGroupWarps];      // per producer warp: any of its 16 samples active
 };
 __device__ __forceinline__ int ws_any(const WsMeta& m) {
-  return m.flag[0] | m.flag[1] | m.flag[2] | m.flag[3] | m.flag[4] | m.flag[5] | m.flag[6] | m.flag[7];
+  int f = 0;
+#pragma unroll
+  for (int i = 0; i < kWsGroupWarps; ++i) f |= m.flag[i];
+  return f;
 }
 
-struct WsTables {            // rows 16w .. 16w+15 are private to producer warp w
-  int4 toff[3][kTile];
-  float4 twgt[3][kTile];
+struct WsTables {            // rows 16w .. 16w+15 are private to producer warp w of the group
+  uint4 toff[3][kTile];      // byte offsets of the 4 texels from the image's first plane (plane included)
+  float4 twgt[3][kTile];     // bilinear weights, pre-scaled by 1/3 (the mean over the planes)
 };
 
 struct WsFwdSmem {
   nfi_mlp::FwdWeights w;
   float a[kNS][2][nfi_mlp::kStageFloats];
-  WsTables tab;
+  WsTables tab[kWsGroups];
   WsMeta meta[kNM];
   uint64_t a_full[kNS], a_empty[kNS], meta_full[kNM], meta_empty[kNM];
   uint64_t d0_full[kNA], h_full[kNA], d1_full[kNA];
@@ -53,76 +82,98 @@ struct WsFwdSmem {
   uint32_t pad;
 };
 
+// inputs of phase 1 for one sample, fetched one tile ahead of their use
+struct WsCoord {
+  float o[3], d[3], z;       // PTS: o is the point itself
+  int sid;
+};
+
+template <bool PTS>
+__device__ __forceinline__ WsCoord ws_load_coord(const Args& a, int b, int t, int row, int per_image) {
+  WsCoord c;
+  int ray;
+  c.sid = sample_and_ray(a, t, row, ray);
+  if (c.sid >= 0) {
+    const int64_t id = (int64_t)b * per_image + c.sid;
+    if (PTS) {
+      c.o[0] = __ldg(a.points + id * 3); c.o[1] = __ldg(a.points + id * 3 + 1); c.o[2] = __ldg(a.points + id * 3 + 2);
+    } else {
+      const int64_t r3 = ((int64_t)b * a.npi + ray) * 3;
+#pragma unroll
+      for (int i = 0; i < 3; ++i) { c.o[i] = __ldg(a.origins + r3 + i); c.d[i] = __ldg(a.dirs + r3 + i); }
+      c.z = __ldg(a.z + id);
+    }
+  }
+  return c;
+}
+
 // phase 1 for the pipelined kernels: writes the producer table + the meta entry
 template <bool PTS, int MODE>
-__device__ __forceinline__ bool ws_phase1(const Args& a, WsTables& tb, WsMeta& mt, int64_t id, int sid, int tid) {
+__device__ __forceinline__ bool ws_phase1(const Args& a, WsTables& tb, WsMeta& mt, const WsCoord& c, int row) {
   float keep = -1.f;
   bool active = false;
-  if (id >= 0) {
+  if (c.sid >= 0) {
     float pt[3];
-    if (PTS) { pt[0] = a.points[id * 3]; pt[1] = a.points[id * 3 + 1]; pt[2] = a.points[id * 3 + 2]; }
-    else {
-      const int64_t ray = id / a.S;
-      const float o[3] = {a.origins[ray * 3], a.origins[ray * 3 + 1], a.origins[ray * 3 + 2]};
-      const float d[3] = {a.dirs[ray * 3], a.dirs[ray * 3 + 1], a.dirs[ray * 3 + 2]};
-      nfi_point(o, d, a.z[id], pt);
-    }
+    if (PTS) { pt[0] = c.o[0]; pt[1] = c.o[1]; pt[2] = c.o[2]; }
+    else nfi_point(c.o, c.d, c.z, pt);
     float x[3];
 #pragma unroll
-    for (int c = 0; c < 3; ++c) x[c] = NFI_DIV(pt[c], a.f.scene_range);
+    for (int i = 0; i < 3; ++i) x[i] = NFI_DIV(pt[i], a.f.scene_range);
     keep = 1.f;
     if (MODE == 0 && (fabsf(x[0]) > 1.f || fabsf(x[1]) > 1.f || fabsf(x[2]) > 1.f)) keep = 0.f;
     active = sample_active(a, keep);
     if (active) {
+      const float third = 1.f / 3.f;
+      const uint32_t plane_texels = (uint32_t)(a.Hp * a.Wp);
 #pragma unroll
       for (int p = 0; p < 3; ++p) {
         const float ix = nfi_unnormalize(x[nfi_plane_axis_a(p)], a.Wp, nullptr);
         const float iy = nfi_unnormalize(x[nfi_plane_axis_b(p)], a.Hp, nullptr);
         NfiFoot f;
         nfi_footprint(ix, iy, a.Wp, a.Hp, f);
-        tb.toff[p][tid] = make_int4((f.y0 * a.Wp + f.x0) * 8, (f.y0 * a.Wp + f.x1) * 8,
-                                    (f.y1 * a.Wp + f.x0) * 8, (f.y1 * a.Wp + f.x1) * 8);
-        tb.twgt[p][tid] = make_float4(f.wnw, f.wne, f.wsw, f.wse);
+        const uint32_t r0 = p * plane_texels + (uint32_t)nfi_texel_row(f.y0, a.bshift, a.nbx);
+        const uint32_t r1 = p * plane_texels + (uint32_t)nfi_texel_row(f.y1, a.bshift, a.nbx);
+        const uint32_t c0 = (uint32_t)nfi_texel_col(f.x0, a.bshift), c1 = (uint32_t)nfi_texel_col(f.x1, a.bshift);
+        tb.toff[p][row] = make_uint4((r0 + c0) * 128u, (r0 + c1) * 128u, (r1 + c0) * 128u, (r1 + c1) * 128u);
+        tb.twgt[p][row] = make_float4(f.wnw * third, f.wne * third, f.wsw * third, f.wse * third);
       }
     }
   }
-  mt.keep[tid] = keep;
-  mt.sid[tid] = sid;
+  mt.keep[row] = keep;
+  mt.sid[row] = c.sid;
   return active;
 }
 
-// phase 2 for the pipelined kernels (256 producer threads, ptid = 0..255)
+__device__ __forceinline__ float4 ws_ldg(const char* base, uint32_t off) {
+  return __ldg(reinterpret_cast<const float4*>(base + off));
+}
+__device__ __forceinline__ void ws_fma4(float4& acc, const float4& v, float w) {
+  acc.x = fmaf(v.x, w, acc.x); acc.y = fmaf(v.y, w, acc.y); acc.z = fmaf(v.z, w, acc.z); acc.w = fmaf(v.w, w, acc.w);
+}
+
+// phase 2 for the pipelined kernels: warp w of a group gathers rows 16w .. 16w+15, 8 lanes per texel
 __device__ __forceinline__ void ws_gather(const Args& a, const WsTables& tb, const WsMeta& mt, float* a_hi,
-                                          float* a_lo, int b, int ptid) {
-  const int lane = ptid & 31, warp = ptid >> 5;
+                                          float* a_lo, int b, int gw, int lane) {
   const int c4 = lane & 7;
-  const float third = 1.f / 3.f;
-  const int plane_f4 = a.Hp * a.Wp * 8;
-  const float4* base = reinterpret_cast<const float4*>(a.planes) + (int64_t)b * 3 * plane_f4 + c4;
+  const char* base = reinterpret_cast<const char*>(a.planes) + (int64_t)b * 3 * a.Hp * a.Wp * 128 + c4 * 16;
 #pragma unroll 2
-  for (int it = 0; it < 4; ++it) {
-    const int s = warp * 16 + it * 4 + (lane >> 3);
+  for (int it = 0; it < kWsRows / 4; ++it) {
+    const int s = gw * kWsRows + it * 4 + (lane >> 3);
     float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
     if (sample_active(a, mt.keep[s])) {
       float4 v[3][4];
       float4 w[3];
 #pragma unroll
       for (int p = 0; p < 3; ++p) {
-        const int4 o = tb.toff[p][s];
+        const uint4 o = tb.toff[p][s];
         w[p] = tb.twgt[p][s];
-        const float4* P = base + p * plane_f4;
-        v[p][0] = __ldg(P + o.x); v[p][1] = __ldg(P + o.y); v[p][2] = __ldg(P + o.z); v[p][3] = __ldg(P + o.w);
+        v[p][0] = ws_ldg(base, o.x); v[p][1] = ws_ldg(base, o.y); v[p][2] = ws_ldg(base, o.z); v[p][3] = ws_ldg(base, o.w);
       }
 #pragma unroll
       for (int p = 0; p < 3; ++p) {
-        float4 e;
-        e.x = fmaf(v[p][3].x, w[p].w, fmaf(v[p][2].x, w[p].z, fmaf(v[p][1].x, w[p].y, v[p][0].x * w[p].x)));
-        e.y = fmaf(v[p][3].y, w[p].w, fmaf(v[p][2].y, w[p].z, fmaf(v[p][1].y, w[p].y, v[p][0].y * w[p].x)));
-        e.z = fmaf(v[p][3].z, w[p].w, fmaf(v[p][2].z, w[p].z, fmaf(v[p][1].z, w[p].y, v[p][0].z * w[p].x)));
-        e.w = fmaf(v[p][3].w, w[p].w, fmaf(v[p][2].w, w[p].z, fmaf(v[p][1].w, w[p].y, v[p][0].w * w[p].x)));
-        acc.x += e.x; acc.y += e.y; acc.z += e.z; acc.w += e.w;
+        ws_fma4(acc, v[p][0], w[p].x); ws_fma4(acc, v[p][1], w[p].y);
+        ws_fma4(acc, v[p][2], w[p].z); ws_fma4(acc, v[p][3], w[p].w);
       }
-      acc.x *= third; acc.y *= third; acc.z *= third; acc.w *= third;
     }
     nfi_mlp::store_feat4(a_hi, a_lo, s, c4, acc);
   }
@@ -140,8 +191,8 @@ field_fwd_ws_kernel(const Args a) {
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   nfi_mlp::load_weights(sm.w, a.f.W0, a.f.b0, a.f.W1, a.f.b1, a.f.n_out);
   if (tid == 0) {
-    for (int i = 0; i < kNS; ++i) { nfi_tc::mbar_init(&sm.a_full[i], kWsProducerWarps); nfi_tc::mbar_init(&sm.a_empty[i], 1); }
-    for (int i = 0; i < kNM; ++i) { nfi_tc::mbar_init(&sm.meta_full[i], kWsProducerWarps); nfi_tc::mbar_init(&sm.meta_empty[i], kWsEpilogueWarps + 1); }
+    for (int i = 0; i < kNS; ++i) { nfi_tc::mbar_init(&sm.a_full[i], kWsGroupWarps); nfi_tc::mbar_init(&sm.a_empty[i], 1); }
+    for (int i = 0; i < kNM; ++i) { nfi_tc::mbar_init(&sm.meta_full[i], kWsGroupWarps); nfi_tc::mbar_init(&sm.meta_empty[i], kWsEpilogueWarps + 1); }
     for (int i = 0; i < kNA; ++i) { nfi_tc::mbar_init(&sm.d0_full[i], 1); nfi_tc::mbar_init(&sm.h_full[i], kWsEpilogueWarps); nfi_tc::mbar_init(&sm.d1_full[i], 1); }
     nfi_tc::mbar_fence_init();
   }
@@ -157,39 +208,88 @@ field_fwd_ws_kernel(const Args a) {
 
   if (warp < kWsProducerWarps) {
     // ------------------------------------------------------------------ producers
-    // every warp owns rows 16w .. 16w+15 of each tile end to end (coords by lanes 0-15, gather by
-    // all 32 lanes): no cross-warp barrier, warps drift apart and cover each other's load latency
-    const int ptid = tid;
-    const int row = warp * 16 + (lane & 15);
-    uint32_t it = 0;
-    for (int b = 0; b < a.B; ++b) {
-      for (int64_t tt = lo; tt < hi; ++tt, ++it) {
-        const uint32_t m = it % kNM, s = it % kNS;
-        WsMeta& mt = sm.meta[m];
-        nfi_tc::mbar_wait(&sm.meta_empty[m], ((it / kNM) & 1) ^ 1);
-        bool active = false;
-        if (lane < 16) {
-          const int sid = sample_in_image(a, (int)tt, row);
-          const int64_t id = sid >= 0 ? (int64_t)b * per_image + sid : -1;
-          active = ws_phase1<PTS, MODE>(a, sm.tab, mt, id, sid, row);
-        }
-        const unsigned wany = __any_sync(0xffffffffu, active);
-        if (lane == 0) { mt.flag[warp] = wany ? 1 : 0; }
-        __syncwarp();
-        if (lane == 0) nfi_tc::mbar_arrive(&sm.meta_full[m]);
-        nfi_tc::mbar_wait(&sm.a_empty[s], ((it / kNS) & 1) ^ 1);
-        if (wany) ws_gather(a, sm.tab, mt, sm.a[s][0], sm.a[s][1], b, ptid);
-        nfi_tc::fence_proxy_async();
-        __syncwarp();
-        if (lane == 0) nfi_tc::mbar_arrive(&sm.a_full[s]);
-      }
+    // every warp owns rows 16w .. 16w+15 of its group's tiles end to end (coords by lanes 0-15,
+    // gather by all 32 lanes): no cross-warp barrier, warps drift apart and cover each other's
+    // load latency; the inputs of the next tile's phase 1 are fetched before this tile's gather
+    const int g = warp / kWsGroupWarps, gw = warp % kWsGroupWarps;
+    const int row = gw * kWsRows + (lane & (kWsRows - 1));
+    const int ntile = (int)(hi - lo);
+    const uint32_t total = (uint32_t)a.B * (uint32_t)ntile;
+    WsTables& tab = sm.tab[g];
+    int b = 0, tl = g;
+    while (tl >= ntile) { tl -= ntile; ++b; }
+    WsCoord cur;
+    cur.sid = -1;
+    if (lane < kWsRows && (uint32_t)g < total) cur = ws_load_coord<PTS>(a, b, (int)lo + tl, row, (int)per_image);
+    for (uint32_t it = g; it < total; it += kWsGroups) {
+      const uint32_t m = it % kNM, s = it % kNS;
+      WsMeta& mt = sm.meta[m];
+      nfi_tc::mbar_wait(&sm.meta_empty[m], ((it / kNM) & 1) ^ 1);
+      if (gw == 0 && lane == 0 && g < 2) NFI_TRACE(g, it, 0);
+      bool active = false;
+      if (lane < kWsRows) active = ws_phase1<PTS, MODE>(a, tab, mt, cur, row);
+      const unsigned wany = __any_sync(0xffffffffu, active);
+      if (lane == 0) { mt.flag[gw] = wany ? 1 : 0; }
+      __syncwarp();
+      if (lane == 0) nfi_tc::mbar_arrive(&sm.meta_full[m]);
+      const int bcur = b;
+      tl += kWsGroups;
+      while (tl >= ntile) { tl -= ntile; ++b; }
+      if (lane < kWsRows && it + kWsGroups < total) cur = ws_load_coord<PTS>(a, b, (int)lo + tl, row, (int)per_image);
+      if (gw == 0 && lane == 0 && g < 2) NFI_TRACE(g, it, 1);
+      nfi_tc::mbar_wait(&sm.a_empty[s], ((it / kNS) & 1) ^ 1);
+      if (gw == 0 && lane == 0 && g < 2) NFI_TRACE(g, it, 2);
+      if (wany) ws_gather(a, tab, mt, sm.a[s][0], sm.a[s][1], bcur, gw, lane);
+      nfi_tc::fence_proxy_async();
+      __syncwarp();
+      if (lane == 0) nfi_tc::mbar_arrive(&sm.a_full[s]);
+      if (gw == 0 && lane == 0 && g < 2) NFI_TRACE(g, it, 3);
     }
   } else if (warp < kWsProducerWarps + kWsEpilogueWarps) {
     // ------------------------------------------------------------------ epilogue
+    // order per active tile i: epilogue 0 of tile i, THEN heads of tile i-1 -- the layer-1 MMAs of
+    // tile i-1 run while this warp is busy with tile i's softplus, so their latency is never exposed
     const int ew = warp - kWsProducerWarps;
     const int row = (ew & 3) * 32 + lane;                       // sample row = TMEM lane
     const uint32_t lane_off = (uint32_t)((ew & 3) * 32) << 16;
     const NfiHeads hd = make_heads(a.f);
+    struct { bool valid; uint32_t c, cph, m, it; int64_t id; float keep; int b; } pend;
+    pend.valid = false;
+    auto finish = [&]() {
+      const uint32_t tl = tmem + pend.c * kAccCols + lane_off;
+      nfi_tc::mbar_wait(&sm.d1_full[pend.c], pend.cph);
+      if (ew == 0 && lane == 0) NFI_TRACE(2, pend.it, 2);
+      nfi_tc::fence_after_sync();
+      if (ew < 4) {
+        float y[nfi_mlp::kY];
+        nfi_mlp::epilogue1_at(sm.w.b1, tl, y);
+        const int64_t id = pend.id;
+        if (id >= 0) {
+          if (MODE == 0) {
+            if (!sample_active(a, pend.keep)) {
+              reinterpret_cast<float4*>(a.out)[id] = make_float4(0.f, 0.f, 0.f, 0.f);
+              if (a.probs) for (int q = 0; q < hd.A; ++q) a.probs[id * hd.A + q] = 0.f;
+            } else {
+              float sigma, rgb[3], probs[NFI_YPAD - 1];
+              nfi_heads_fwd(hd, y, pend.keep, a.palette ? a.palette + (int64_t)pend.b * hd.A * 3 : nullptr, sigma, rgb, probs);
+              reinterpret_cast<float4*>(a.out)[id] = make_float4(sigma, rgb[0], rgb[1], rgb[2]);
+              if (a.probs) {
+#pragma unroll
+                for (int q = 0; q < NFI_YPAD - 1; ++q) if (q < hd.A) a.probs[id * hd.A + q] = probs[q];
+              }
+            }
+          } else {
+#pragma unroll
+            for (int o = 0; o < NFI_YPAD; ++o) if (o < a.f.n_out) a.out[id * a.f.n_out + o] = y[o];
+          }
+        }
+      }
+      nfi_tc::fence_before_sync();
+      __syncwarp();
+      if (lane == 0) nfi_tc::mbar_arrive(&sm.meta_empty[pend.m]);
+      if (ew == 0 && lane == 0) NFI_TRACE(2, pend.it, 3);
+      pend.valid = false;
+    };
     uint32_t it = 0, act = 0;
     for (int b = 0; b < a.B; ++b) {
       for (int64_t tt = lo; tt < hi; ++tt, ++it) {
@@ -201,48 +301,28 @@ field_fwd_ws_kernel(const Args a) {
         const int64_t id = sid >= 0 ? (int64_t)b * per_image + sid : -1;
         if (ws_any(mt)) {
           const uint32_t c = act % kNA, cph = (act / kNA) & 1;
-          const uint32_t tl = tmem + c * kAccCols + lane_off;
           nfi_tc::mbar_wait(&sm.d0_full[c], cph);
+          if (ew == 0 && lane == 0) NFI_TRACE(2, it, 0);
           nfi_tc::fence_after_sync();
-          nfi_mlp::epilogue0_at<2>(sm.w.b0, tl, (ew >> 2) * 32);
+          nfi_mlp::epilogue0_at<2>(sm.w.b0, tmem + c * kAccCols + lane_off, (ew >> 2) * 32);
           nfi_tc::fence_before_sync();
           __syncwarp();
           if (lane == 0) nfi_tc::mbar_arrive(&sm.h_full[c]);
-          nfi_tc::mbar_wait(&sm.d1_full[c], cph);
-          nfi_tc::fence_after_sync();
-          if (ew < 4) {
-            float y[nfi_mlp::kY];
-            nfi_mlp::epilogue1_at(sm.w.b1, tl, y);
-            if (id >= 0) {
-              if (MODE == 0) {
-                if (!sample_active(a, keep)) {
-                  reinterpret_cast<float4*>(a.out)[id] = make_float4(0.f, 0.f, 0.f, 0.f);
-                  if (a.probs) for (int q = 0; q < hd.A; ++q) a.probs[id * hd.A + q] = 0.f;
-                } else {
-                  float sigma, rgb[3], probs[NFI_YPAD - 1];
-                  nfi_heads_fwd(hd, y, keep, a.palette ? a.palette + (int64_t)b * hd.A * 3 : nullptr, sigma, rgb, probs);
-                  reinterpret_cast<float4*>(a.out)[id] = make_float4(sigma, rgb[0], rgb[1], rgb[2]);
-                  if (a.probs) {
-#pragma unroll
-                    for (int q = 0; q < NFI_YPAD - 1; ++q) if (q < hd.A) a.probs[id * hd.A + q] = probs[q];
-                  }
-                }
-              } else {
-#pragma unroll
-                for (int o = 0; o < NFI_YPAD; ++o) if (o < a.f.n_out) a.out[id * a.f.n_out + o] = y[o];
-              }
-            }
-          }
-          nfi_tc::fence_before_sync();
+          if (ew == 0 && lane == 0) NFI_TRACE(2, it, 1);
+          if (pend.valid) finish();
+          pend.valid = true; pend.it = it; pend.c = c; pend.cph = cph; pend.m = m; pend.id = id; pend.keep = keep; pend.b = b;
           ++act;
-        } else if (ew < 4 && MODE == 0 && id >= 0) {      // whole tile outside the box
-          reinterpret_cast<float4*>(a.out)[id] = make_float4(0.f, 0.f, 0.f, 0.f);
-          if (a.probs) for (int q = 0; q < hd.A; ++q) a.probs[id * hd.A + q] = 0.f;
+        } else {
+          if (ew < 4 && MODE == 0 && id >= 0) {             // whole tile outside the box
+            reinterpret_cast<float4*>(a.out)[id] = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (a.probs) for (int q = 0; q < hd.A; ++q) a.probs[id * hd.A + q] = 0.f;
+          }
+          __syncwarp();
+          if (lane == 0) nfi_tc::mbar_arrive(&sm.meta_empty[m]);
         }
-        __syncwarp();
-        if (lane == 0) nfi_tc::mbar_arrive(&sm.meta_empty[m]);
       }
     }
+    if (pend.valid) finish();
   } else if (lane == 0) {
     // ------------------------------------------------------------------ MMA issuer (one thread)
     uint32_t it = 0, act = 0;
@@ -256,16 +336,20 @@ field_fwd_ws_kernel(const Args a) {
         nfi_tc::mbar_arrive(&sm.meta_empty[m]);
         const uint32_t s = it % kNS, c = act % kNA;
         nfi_tc::mbar_wait(&sm.a_full[s], (it / kNS) & 1);
+        NFI_TRACE(3, it, 0);
         if (!any) { nfi_tc::mbar_arrive(&sm.a_empty[s]); continue; }
         nfi_tc::fence_after_sync();
         nfi_mlp::issue_layer0_at(sm.w, sm.a[s][0], sm.a[s][1], tmem + c * kAccCols);
         nfi_tc::mma_commit(&sm.a_empty[s]);
         nfi_tc::mma_commit(&sm.d0_full[c]);
+        NFI_TRACE(3, it, 1);
         if (pend) {
           nfi_tc::mbar_wait(&sm.h_full[pc], pph);
+          NFI_TRACE(3, it, 2);
           nfi_tc::fence_after_sync();
           nfi_mlp::issue_layer1_at(sm.w, tmem + pc * kAccCols);
           nfi_tc::mma_commit(&sm.d1_full[pc]);
+          NFI_TRACE(3, it, 3);
         }
         pend = true; pc = c; pph = (act / kNA) & 1;
         ++act;

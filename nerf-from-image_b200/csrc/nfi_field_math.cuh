@@ -13,6 +13,21 @@
 #endif
 
 // ---------------------------------------------------------------------------------------------
+// Texel order of a channels-last plane in HBM.  When both plane sides are multiples of 8 the plane is
+// stored as contiguous 8 x 8 texel blocks (8 KB each, bshift = 3): the 2 x 2 bilinear footprint and the
+// ~9 x 17 texel neighbourhood of a pixel-block tile then cover a few contiguous 8 KB runs instead of
+// 9 rows one power-of-two stride apart (which alias in L1).  Otherwise row-major (bshift = 0).
+//   index(y, x) = nfi_texel_row(y) + nfi_texel_col(x)        (texel units; * 32 floats)
+// ---------------------------------------------------------------------------------------------
+NFI_HD int nfi_plane_bshift(int Hp, int Wp) { return (Hp % 8 == 0 && Wp % 8 == 0) ? 3 : 0; }
+NFI_HD int nfi_texel_row(int y, int bshift, int nbx) {
+  return (((y >> bshift) * nbx) << (2 * bshift)) + ((y & ((1 << bshift) - 1)) << bshift);
+}
+NFI_HD int nfi_texel_col(int x, int bshift) {
+  return ((x >> bshift) << (2 * bshift)) + (x & ((1 << bshift) - 1));
+}
+
+// ---------------------------------------------------------------------------------------------
 // F.grid_sample(bilinear, border, align_corners=True), one axis   (ATen GridSampler.h)
 //   i = ((g + 1) / 2) * (size - 1); clamp to [0, size-1]; d i / d g = (size-1)/2 strictly inside
 // ---------------------------------------------------------------------------------------------

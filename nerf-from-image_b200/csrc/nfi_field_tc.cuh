@@ -26,9 +26,10 @@ constexpr int kThreads = 256;
 
 struct Args {
   NfiField f;
-  const float* planes;    // [B,3,Hp,Wp,32]
+  const float* planes;    // [B,3,Hp*Wp,32], texel order of nfi_field_math.cuh (nfi_texel_row / _col)
   const float* palette;   // [B,A,3]
   int B, Hp, Wp;
+  int bshift, nbx;        // texel order: block shift (3 or 0) and blocks per plane row
   const float* origins; const float* dirs; const float* z; const float* points;
   int64_t npi;            // rays (or points) per image
   int S;
@@ -55,6 +56,22 @@ __device__ __forceinline__ int sample_in_image(const Args& a, int t, int tid) {
   const int by = blk / a.blocks_x, bx = blk - by * a.blocks_x;
   const int py = tid >> 4, px = tid & 15;
   const int ray = (by * 8 + py) * a.img_w + bx * 16 + px;
+  return ray * a.S + k;
+}
+
+// same mapping, also returning the ray index within the image (no 64-bit division on the hot path)
+__device__ __forceinline__ int sample_and_ray(const Args& a, int t, int tid, int& ray) {
+  if (a.blocks_x == 0) {
+    const int64_t local = (int64_t)t * kTile + tid;
+    if (local >= a.npi * a.S) { ray = 0; return -1; }
+    ray = (int)local / a.S;
+    return (int)local;
+  }
+  const int blk = t / a.S;
+  const int k = t - blk * a.S;
+  const int by = blk / a.blocks_x, bx = blk - by * a.blocks_x;
+  const int py = tid >> 4, px = tid & 15;
+  ray = (by * 8 + py) * a.img_w + bx * 16 + px;
   return ray * a.S + k;
 }
 
@@ -96,8 +113,9 @@ __device__ __forceinline__ void phase1(const Args& a, Tables& t, int64_t id, int
         const float iy = nfi_unnormalize(x[nfi_plane_axis_b(p)], a.Hp, &my);
         NfiFoot f;
         nfi_footprint(ix, iy, a.Wp, a.Hp, f);
-        t.toff[p][tid] = make_int4((f.y0 * a.Wp + f.x0) * 8, (f.y0 * a.Wp + f.x1) * 8,
-                                   (f.y1 * a.Wp + f.x0) * 8, (f.y1 * a.Wp + f.x1) * 8);
+        const int r0 = nfi_texel_row(f.y0, a.bshift, a.nbx), r1 = nfi_texel_row(f.y1, a.bshift, a.nbx);
+        const int c0 = nfi_texel_col(f.x0, a.bshift), c1 = nfi_texel_col(f.x1, a.bshift);
+        t.toff[p][tid] = make_int4((r0 + c0) * 8, (r0 + c1) * 8, (r1 + c0) * 8, (r1 + c1) * 8);
         t.twgt[p][tid] = make_float4(f.wnw, f.wne, f.wsw, f.wse);
         if (DER) {
           // ATen zeroes out-of-range neighbours (within_bounds_2d) in the coordinate gradient; that

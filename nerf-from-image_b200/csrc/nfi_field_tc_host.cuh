@@ -23,7 +23,7 @@ static inline int fill_args(Args& a, const char* who, const NfiField* field, con
   NFI_REQUIRE(planes_cl, NFI_ERR_BAD_ARG, "%s: NULL planes", who);
   NFI_REQUIRE(nfi_aligned16(planes_cl), NFI_ERR_ALIGNMENT, "%s: planes must be 16-byte aligned", who);
   NFI_REQUIRE(B > 0 && Hp >= 2 && Wp >= 2 && n_per_image > 0 && S >= 1, NFI_ERR_BAD_ARG, "%s: bad sizes", who);
-  NFI_REQUIRE((int64_t)Hp * Wp * 8 < (int64_t)1 << 31, NFI_ERR_UNSUPPORTED, "%s: plane too large", who);
+  NFI_REQUIRE((int64_t)Hp * Wp * 3 * 128 < (int64_t)1 << 32, NFI_ERR_UNSUPPORTED, "%s: plane too large", who);
   NFI_REQUIRE(n_per_image * S < ((int64_t)1 << 31) - kTile, NFI_ERR_UNSUPPORTED, "%s: more than 2^31 samples per image", who);
   NFI_REQUIRE(mode == 0 || mode == 1, NFI_ERR_BAD_ARG, "%s: mode must be 0 or 1", who);
   NFI_REQUIRE(points || (origins && dirs && z), NFI_ERR_BAD_ARG, "%s: need points or origins/dirs/z", who);
@@ -31,6 +31,7 @@ static inline int fill_args(Args& a, const char* who, const NfiField* field, con
   NFI_REQUIRE(mode == 1 || field->attention_values == 0 || palette, NFI_ERR_BAD_ARG, "%s: attention head needs a palette", who);
   a.f = *field;
   a.planes = planes_cl; a.palette = palette; a.B = B; a.Hp = Hp; a.Wp = Wp;
+  a.bshift = nfi_plane_bshift(Hp, Wp); a.nbx = Wp >> a.bshift;
   a.origins = origins; a.dirs = dirs; a.z = z; a.points = points;
   a.npi = n_per_image; a.S = S; a.img_w = img_w; a.skip_oob = 0;
   a.n_total = (int64_t)B * n_per_image * S;
