@@ -1,0 +1,83 @@
+"""Per-image sharding of the render path across ranks.
+
+The path has no exchange step: every image -- planes, palette, pose, rays, samples, outputs and
+gradients -- is independent (run.py scatters along dim 0 through nn.DataParallel, run.py:636-644).
+Rank r of G owns images [r*B/G, (r+1)*B/G); there is NO collective on the data path.  The helpers
+here are the host-side plumbing around that: shard bounds, slicing a batch of render arguments, and
+the one collective the inversion loop has -- gathering per-image report tensors at the end
+(run.py:2020-2027).  Works on any torch.distributed backend (NCCL on the GPUs, gloo in the CPU tests).
+"""
+from typing import Any, Dict, Optional, Sequence, Tuple
+
+import torch
+import torch.distributed as dist
+
+
+def rank_world() -> Tuple[int, int]:
+    if dist.is_available() and dist.is_initialized():
+        return dist.get_rank(), dist.get_world_size()
+    return 0, 1
+
+
+def shard_range(batch: int, rank: Optional[int] = None, world: Optional[int] = None) -> Tuple[int, int]:
+    """Images [lo, hi) owned by `rank`.  Ragged batches are allowed: the first batch % world ranks
+    get one extra image; a rank may own nothing (lo == hi) when batch < world."""
+    if rank is None or world is None:
+        rank, world = rank_world()
+    if batch < 0 or world <= 0 or not 0 <= rank < world:
+        raise ValueError("shard_range: bad batch/rank/world = %r/%r/%r" % (batch, rank, world))
+    base, extra = divmod(batch, world)
+    lo = rank * base + min(rank, extra)
+    return lo, lo + base + (1 if rank < extra else 0)
+
+
+def shard_batch(args: Dict[str, Any], batch: int, rank: Optional[int] = None,
+                world: Optional[int] = None) -> Dict[str, Any]:
+    """Slice every per-image tensor of a dict of render arguments (leading dim == batch) to this
+    rank's images; 0-dim tensors (the perspective-eval focal, eval_kitti_persp.py:948), None and
+    non-tensors are shared by all ranks, as nn.DataParallel's scatter does."""
+    lo, hi = shard_range(batch, rank, world)
+    out = {}
+    for k, v in args.items():
+        if torch.is_tensor(v) and v.dim() > 0 and v.shape[0] == batch:
+            out[k] = v[lo:hi]
+        else:
+            out[k] = v
+    return out
+
+
+def gather_report(local: torch.Tensor, batch: int) -> torch.Tensor:
+    """all_gather of per-image report tensors (ws, pose parameters, PSNR ...; run.py:2020-2027) back
+    into batch order.  `local` holds this rank's images [hi-lo, ...]; shards may be ragged."""
+    rank, world = rank_world()
+    if world == 1:
+        return local
+    lo, hi = shard_range(batch, rank, world)
+    if local.shape[0] != hi - lo:
+        raise ValueError("gather_report: rank %d owns %d images, got %d" % (rank, hi - lo, local.shape[0]))
+    width = max(shard_range(batch, r, world)[1] - shard_range(batch, r, world)[0] for r in range(world))
+    pad = local.new_zeros((width,) + tuple(local.shape[1:]))
+    pad[: hi - lo] = local
+    parts = [torch.empty_like(pad) for _ in range(world)]
+    dist.all_gather(parts, pad.contiguous())
+    sizes = [shard_range(batch, r, world) for r in range(world)]
+    return torch.cat([p[: b - a] for p, (a, b) in zip(parts, sizes)], dim=0)
+
+
+def max_over_ranks(value: float, device: Optional[torch.device] = None) -> float:
+    """Timing rule of bench.py: a multi-GPU number is the max over ranks."""
+    rank, world = rank_world()
+    if world == 1:
+        return float(value)
+    t = torch.tensor([float(value)], dtype=torch.float64, device=device or "cpu")
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    return float(t.item())
+
+
+def render_sharded(render_fn, batch: int, per_image: Dict[str, Any], shared: Sequence[Any] = ()):
+    """Run `render_fn(*shared, **shard)` on this rank's images only and return (lo, hi, outputs).
+    No collective: the caller keeps its slice (inversion) or reduces its own loss."""
+    lo, hi = shard_range(batch)
+    if hi == lo:
+        return lo, hi, None
+    return lo, hi, render_fn(*shared, **shard_batch(per_image, batch))
