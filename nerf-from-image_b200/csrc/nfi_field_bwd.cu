@@ -3,14 +3,13 @@
 // tile, the MLP adjoint runs on tcgen05 (nfi_mlp_tc.cuh), and the feature gradient is scattered
 // into the channels-last gradient planes with red.global.add.v4.f32 (one 128-byte line per texel
 // and 8 lanes).  Summation order into the planes is not deterministic (fp32 atomics).
+#include <stdio.h>
+#include <stdlib.h>
+
+#include "nfi_field_bwd_ws.cuh"
 #include "nfi_field_tc_host.cuh"
 
 namespace nfi_ftc {
-
-__device__ __forceinline__ void red_add_v4(float* addr, float a, float b, float c, float d) {
-  asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(addr), "f"(a), "f"(b), "f"(c), "f"(d)
-               : "memory");
-}
 
 constexpr int kDfLd = 36;            // d feature tile row stride (floats): conflict-free float4 rows
 constexpr int kNPal = 3 * (NFI_YPAD - 1);
@@ -268,9 +267,52 @@ extern "C" int nfi_field_bwd(const NfiField* field, const float* planes_cl, cons
   NFI_REQUIRE(!g_planes_cl || nfi_aligned16(g_planes_cl), NFI_ERR_ALIGNMENT, "nfi_field_bwd: g_planes must be 16-byte aligned");
   a.g_out = g_out; a.g_planes = g_planes_cl; a.g_palette = (mode == 0) ? g_palette : nullptr;
   a.g_points = g_points; a.g_params = g_params;
+  cudaStream_t st = nfi_cu(stream);
+  const bool wp = g_points != nullptr;
+  static const bool old_kernel = getenv("NFI_BWD_OLD") != nullptr;     // development A/B switch
+  if (!old_kernel) {
+    const int grid = field_grid_chunks(a);
+    const int smem = (int)sizeof(BwSmem);
+#define NFI_LAUNCH_BWS(P, M, W)                                                                         \
+  do {                                                                                                  \
+    cudaError_t e = cudaFuncSetAttribute(field_bwd_ws_kernel<P, M, W>,                                  \
+                                         cudaFuncAttributeMaxDynamicSharedMemorySize, smem);            \
+    NFI_REQUIRE(e == cudaSuccess, NFI_ERR_LAUNCH, "nfi_field_bwd: cudaFuncSetAttribute: %s",            \
+                cudaGetErrorString(e));                                                                 \
+    field_bwd_ws_kernel<P, M, W><<<grid, kBwThreads, smem, st>>>(a);                                    \
+  } while (0)
+    if (points) {
+      if (mode == 0) { if (wp) NFI_LAUNCH_BWS(true, 0, true); else NFI_LAUNCH_BWS(true, 0, false); }
+      else           { if (wp) NFI_LAUNCH_BWS(true, 1, true); else NFI_LAUNCH_BWS(true, 1, false); }
+    } else {
+      if (mode == 0) { if (wp) NFI_LAUNCH_BWS(false, 0, true); else NFI_LAUNCH_BWS(false, 0, false); }
+      else           { if (wp) NFI_LAUNCH_BWS(false, 1, true); else NFI_LAUNCH_BWS(false, 1, false); }
+    }
+#undef NFI_LAUNCH_BWS
+    NFI_CHECK_LAUNCH("field_bwd_ws_kernel");
+#ifdef NFI_WS_TRACE
+    if (const char* path = getenv("NFI_WS_TRACE_FILE")) {       // developer builds only: blocking dump
+      static int launch = 0;
+      static long long host[kBtRoles * kBtN * kBtEv];
+      cudaStreamSynchronize(st);
+      cudaMemcpyFromSymbol(host, g_bw_trace, sizeof(host));
+      char name[512];
+      snprintf(name, sizeof(name), "%s.bwd.%d", path, launch++ % 2);
+      if (FILE* fp = fopen(name, "w")) {
+        for (int r = 0; r < kBtRoles; ++r)
+          for (int t = 0; t < kBtN; ++t) {
+            fprintf(fp, "%d %d", r, t);
+            for (int e = 0; e < kBtEv; ++e) fprintf(fp, " %lld", host[(r * kBtN + t) * kBtEv + e]);
+            fprintf(fp, "\n");
+          }
+        fclose(fp);
+      }
+    }
+#endif
+    return NFI_OK;
+  }
   const int grid = field_grid(a, 2);
   const int smem = (int)sizeof(BwdSmem);
-  cudaStream_t st = nfi_cu(stream);
 #define NFI_LAUNCH_BWD(P, M, W)                                                                         \
   do {                                                                                                  \
     cudaError_t e = cudaFuncSetAttribute(field_bwd_tc_kernel<P, M, W>,                                  \
@@ -279,7 +321,6 @@ extern "C" int nfi_field_bwd(const NfiField* field, const float* planes_cl, cons
                 cudaGetErrorString(e));                                                                 \
     field_bwd_tc_kernel<P, M, W><<<grid, kThreads, smem, st>>>(a);                                      \
   } while (0)
-  const bool wp = g_points != nullptr;
   if (points) {
     if (mode == 0) { if (wp) NFI_LAUNCH_BWD(true, 0, true); else NFI_LAUNCH_BWD(true, 0, false); }
     else           { if (wp) NFI_LAUNCH_BWD(true, 1, true); else NFI_LAUNCH_BWD(true, 1, false); }

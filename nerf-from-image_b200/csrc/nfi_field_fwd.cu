@@ -80,7 +80,7 @@ extern "C" int nfi_field_fwd(const NfiField* field, const float* planes_cl, cons
   a.out = out; a.probs = probs_out; a.skip_oob = skip_oob;
   cudaStream_t st = nfi_cu(stream);
   {
-    const int grid = field_grid(a, 1);
+    const int grid = field_grid_chunks(a);
     const int smem = (int)sizeof(WsFwdSmem);
 #define NFI_LAUNCH_WS(P, M)                                                               \
   do {                                                                                    \

@@ -203,8 +203,8 @@ field_fwd_ws_kernel(const Args a) {
   nfi_tc::fence_after_sync();
   const uint32_t tmem = sm.tmem_base;
   const int64_t per_image = a.npi * a.S;
-  int64_t lo, hi;
-  cta_tile_range(a.tiles_per_image, lo, hi);
+  const TileMap tm = cta_tile_map(a.tiles_per_image);
+  const int ntile = tm.ntile;
 
   if (warp < kWsProducerWarps) {
     // ------------------------------------------------------------------ producers
@@ -213,14 +213,13 @@ field_fwd_ws_kernel(const Args a) {
     // load latency; the inputs of the next tile's phase 1 are fetched before this tile's gather
     const int g = warp / kWsGroupWarps, gw = warp % kWsGroupWarps;
     const int row = gw * kWsRows + (lane & (kWsRows - 1));
-    const int ntile = (int)(hi - lo);
     const uint32_t total = (uint32_t)a.B * (uint32_t)ntile;
     WsTables& tab = sm.tab[g];
     int b = 0, tl = g;
     while (tl >= ntile) { tl -= ntile; ++b; }
     WsCoord cur;
     cur.sid = -1;
-    if (lane < kWsRows && (uint32_t)g < total) cur = ws_load_coord<PTS>(a, b, (int)lo + tl, row, (int)per_image);
+    if (lane < kWsRows && (uint32_t)g < total) cur = ws_load_coord<PTS>(a, b, tm.tile(tl), row, (int)per_image);
     for (uint32_t it = g; it < total; it += kWsGroups) {
       const uint32_t m = it % kNM, s = it % kNS;
       WsMeta& mt = sm.meta[m];
@@ -235,7 +234,7 @@ field_fwd_ws_kernel(const Args a) {
       const int bcur = b;
       tl += kWsGroups;
       while (tl >= ntile) { tl -= ntile; ++b; }
-      if (lane < kWsRows && it + kWsGroups < total) cur = ws_load_coord<PTS>(a, b, (int)lo + tl, row, (int)per_image);
+      if (lane < kWsRows && it + kWsGroups < total) cur = ws_load_coord<PTS>(a, b, tm.tile(tl), row, (int)per_image);
       if (gw == 0 && lane == 0 && g < 2) NFI_TRACE(g, it, 1);
       nfi_tc::mbar_wait(&sm.a_empty[s], ((it / kNS) & 1) ^ 1);
       if (gw == 0 && lane == 0 && g < 2) NFI_TRACE(g, it, 2);
@@ -292,7 +291,7 @@ field_fwd_ws_kernel(const Args a) {
     };
     uint32_t it = 0, act = 0;
     for (int b = 0; b < a.B; ++b) {
-      for (int64_t tt = lo; tt < hi; ++tt, ++it) {
+      for (int tl = 0; tl < ntile; ++tl, ++it) {
         const uint32_t m = it % kNM;
         const WsMeta& mt = sm.meta[m];
         nfi_tc::mbar_wait(&sm.meta_full[m], (it / kNM) & 1);
@@ -323,33 +322,44 @@ field_fwd_ws_kernel(const Args a) {
       }
     }
     if (pend.valid) finish();
-  } else if (lane == 0) {
-    // ------------------------------------------------------------------ MMA issuer (one thread)
+  } else {
+    // ------------------------------------------------------------------ MMA issuer
+    // the whole warp walks the loop (converged); one elected lane issues MMAs, commits and arrives
     uint32_t it = 0, act = 0;
     bool pend = false;
     uint32_t pc = 0, pph = 0;
     for (int b = 0; b < a.B; ++b) {
-      for (int64_t tt = lo; tt < hi; ++tt, ++it) {
+      for (int tl = 0; tl < ntile; ++tl, ++it) {
         const uint32_t m = it % kNM;
         nfi_tc::mbar_wait(&sm.meta_full[m], (it / kNM) & 1);
         const int any = ws_any(sm.meta[m]);
-        nfi_tc::mbar_arrive(&sm.meta_empty[m]);
+        __syncwarp();
+        if (nfi_tc::elect_one()) nfi_tc::mbar_arrive(&sm.meta_empty[m]);
         const uint32_t s = it % kNS, c = act % kNA;
         nfi_tc::mbar_wait(&sm.a_full[s], (it / kNS) & 1);
-        NFI_TRACE(3, it, 0);
-        if (!any) { nfi_tc::mbar_arrive(&sm.a_empty[s]); continue; }
+        if (lane == 0) NFI_TRACE(3, it, 0);
+        if (!any) {
+          if (nfi_tc::elect_one()) nfi_tc::mbar_arrive(&sm.a_empty[s]);
+          continue;
+        }
         nfi_tc::fence_after_sync();
-        nfi_mlp::issue_layer0_at(sm.w, sm.a[s][0], sm.a[s][1], tmem + c * kAccCols);
-        nfi_tc::mma_commit(&sm.a_empty[s]);
-        nfi_tc::mma_commit(&sm.d0_full[c]);
-        NFI_TRACE(3, it, 1);
+        if (nfi_tc::elect_one()) {
+          nfi_mlp::issue_layer0_at(sm.w, sm.a[s][0], sm.a[s][1], tmem + c * kAccCols);
+          nfi_tc::mma_commit(&sm.a_empty[s]);
+          nfi_tc::mma_commit(&sm.d0_full[c]);
+        }
+        __syncwarp();
+        if (lane == 0) NFI_TRACE(3, it, 1);
         if (pend) {
           nfi_tc::mbar_wait(&sm.h_full[pc], pph);
-          NFI_TRACE(3, it, 2);
+          if (lane == 0) NFI_TRACE(3, it, 2);
           nfi_tc::fence_after_sync();
-          nfi_mlp::issue_layer1_at(sm.w, tmem + pc * kAccCols);
-          nfi_tc::mma_commit(&sm.d1_full[pc]);
-          NFI_TRACE(3, it, 3);
+          if (nfi_tc::elect_one()) {
+            nfi_mlp::issue_layer1_at(sm.w, tmem + pc * kAccCols);
+            nfi_tc::mma_commit(&sm.d1_full[pc]);
+          }
+          __syncwarp();
+          if (lane == 0) NFI_TRACE(3, it, 3);
         }
         pend = true; pc = c; pph = (act / kNA) & 1;
         ++act;
@@ -358,8 +368,11 @@ field_fwd_ws_kernel(const Args a) {
     if (pend) {
       nfi_tc::mbar_wait(&sm.h_full[pc], pph);
       nfi_tc::fence_after_sync();
-      nfi_mlp::issue_layer1_at(sm.w, tmem + pc * kAccCols);
-      nfi_tc::mma_commit(&sm.d1_full[pc]);
+      if (nfi_tc::elect_one()) {
+        nfi_mlp::issue_layer1_at(sm.w, tmem + pc * kAccCols);
+        nfi_tc::mma_commit(&sm.d1_full[pc]);
+      }
+      __syncwarp();
     }
   }
   nfi_tc::fence_before_sync();

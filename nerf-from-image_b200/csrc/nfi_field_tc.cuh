@@ -176,6 +176,33 @@ __device__ __forceinline__ NfiHeads make_heads(const NfiField& f) {
   return hd;
 }
 
+// Interleaved static partition of one image's tiles over the grid (warp-specialised kernels): tiles
+// are dealt out in chunks of kChunk consecutive tiles (= depth steps of one pixel block: L1 reuse
+// inside a chunk), chunk q to CTA q % grid -- every CTA gets pixel blocks from all over the image,
+// so empty (out-of-box) regions and dense ones are shared evenly.
+constexpr int kChunk = 8;
+struct TileMap {
+  int ntile;      // tiles of this CTA per image
+  int stride;     // grid size in tiles (gridDim.x * kChunk)
+  int first;      // first tile of this CTA
+  __device__ __forceinline__ int tile(int l) const { return first + (l / kChunk) * stride + (l % kChunk); }
+};
+__device__ __forceinline__ TileMap cta_tile_map(int64_t tiles) {
+  TileMap m;
+  const int nchunks = (int)((tiles + kChunk - 1) / kChunk);
+  const int c = blockIdx.x, g = gridDim.x;
+  const int mine = c < nchunks ? (nchunks - c + g - 1) / g : 0;
+  m.stride = g * kChunk;
+  m.first = c * kChunk;
+  m.ntile = 0;
+  if (mine > 0) {
+    const int last = c + (mine - 1) * g;                     // only the image's last chunk can be short
+    const int64_t left = tiles - (int64_t)last * kChunk;
+    m.ntile = (mine - 1) * kChunk + (int)(left < kChunk ? left : kChunk);
+  }
+  return m;
+}
+
 // static partition of one image's tiles over the grid: CTA c gets [lo, hi)
 __device__ __forceinline__ void cta_tile_range(int64_t tiles, int64_t& lo, int64_t& hi) {
   lo = tiles * blockIdx.x / gridDim.x;

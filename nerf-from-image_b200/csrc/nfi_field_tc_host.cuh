@@ -24,7 +24,7 @@ static inline int fill_args(Args& a, const char* who, const NfiField* field, con
   NFI_REQUIRE(nfi_aligned16(planes_cl), NFI_ERR_ALIGNMENT, "%s: planes must be 16-byte aligned", who);
   NFI_REQUIRE(B > 0 && Hp >= 2 && Wp >= 2 && n_per_image > 0 && S >= 1, NFI_ERR_BAD_ARG, "%s: bad sizes", who);
   NFI_REQUIRE((int64_t)Hp * Wp * 3 * 128 < (int64_t)1 << 32, NFI_ERR_UNSUPPORTED, "%s: plane too large", who);
-  NFI_REQUIRE(n_per_image * S < ((int64_t)1 << 31) - kTile, NFI_ERR_UNSUPPORTED, "%s: more than 2^31 samples per image", who);
+  NFI_REQUIRE(n_per_image * S < ((int64_t)1 << 31) - 2 * kTile * kChunk, NFI_ERR_UNSUPPORTED, "%s: more than 2^31 samples per image", who);
   NFI_REQUIRE(mode == 0 || mode == 1, NFI_ERR_BAD_ARG, "%s: mode must be 0 or 1", who);
   NFI_REQUIRE(points || (origins && dirs && z), NFI_ERR_BAD_ARG, "%s: need points or origins/dirs/z", who);
   NFI_REQUIRE(!points || S == 1, NFI_ERR_BAD_ARG, "%s: explicit points need S = 1", who);
@@ -44,6 +44,14 @@ static inline int fill_args(Args& a, const char* who, const NfiField* field, con
   a.out = nullptr; a.probs = nullptr; a.g_out = nullptr;
   a.g_planes = a.g_palette = a.g_points = a.g_params = nullptr;
   return NFI_OK;
+}
+
+// grid of the warp-specialised kernels: one CTA per SM, never more CTAs than tile chunks of one image
+static inline int field_grid_chunks(const Args& a) {
+  const int64_t chunks = (a.tiles_per_image + kChunk - 1) / kChunk;
+  const int64_t cap = nfi_sm_count();
+  const int64_t g = chunks < cap ? chunks : cap;
+  return (int)(g < 1 ? 1 : g);
 }
 
 // persistent grid: ctas_per_sm CTAs on every SM, never more CTAs than tiles of one image
