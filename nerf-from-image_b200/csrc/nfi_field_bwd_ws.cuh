@@ -27,7 +27,11 @@
 
 namespace nfi_ftc {
 
-constexpr int kBwPS = 8;                 // gather / scatter warps
+#ifndef NFI_BW_PS
+#define NFI_BW_PS 8
+#endif
+constexpr int kBwPS = NFI_BW_PS;         // gather / scatter warps (8 or 16)
+constexpr int kBwRows = kTile / kBwPS;   // rows of a tile owned by one of them
 constexpr int kBwE = 8;                  // epilogue warps (2 groups of 4)
 constexpr int kBwThreads = (kBwPS + kBwE + 1) * 32;     // 544
 constexpr int kBwNT = 3;                 // table ring: tiles it, it-1, it-2
@@ -68,7 +72,7 @@ struct BwSmem {
   nfi_mlp::BwdWeights bw;
   float a[2][2][nfi_mlp::kStageFloats];
   BwTable tab[kBwNT];
-  float df[kBwPS][16 * kBwDfLd];
+  float df[kBwPS][kBwRows * kBwDfLd];
   BwMeta meta[kBwNM];
   float pal[kBwE][48];
   BwIn in[kBwPS];
@@ -87,7 +91,7 @@ __device__ __forceinline__ int bw_any(const BwMeta& m) {
 
 // rows of gather/scatter warp w: the 16 TMEM lanes [16 (w >> 2), +16) of lane quarter w & 3, so the
 // warp can read its rows of dF with tcgen05.ld (a warp only reaches the quarter warp_id % 4)
-__device__ __forceinline__ int bw_row(int w, int i) { return 32 * (w & 3) + 16 * (w >> 2) + i; }
+__device__ __forceinline__ int bw_row(int w, int i) { return 32 * (w & 3) + kBwRows * (w >> 2) + i; }
 
 __device__ __forceinline__ void cp_async4(void* dst, const void* src) {
   asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" :: "r"(nfi_tc::smem_u32(dst)), "l"(src) : "memory");
@@ -198,7 +202,7 @@ __device__ __forceinline__ void bw_gather(const Args& a, const BwTable& tb, floa
   const float third = 1.f / 3.f;
   const char* base = reinterpret_cast<const char*>(a.planes) + (int64_t)b * 3 * a.Hp * a.Wp * 128 + c4 * 16;
 #pragma unroll 2
-  for (int it = 0; it < 4; ++it) {
+  for (int it = 0; it < kBwRows / 4; ++it) {
     const int s = bw_row(w, it * 4 + (lane >> 3));
     float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
     if (tb.keep[s] >= 0.f) {
@@ -230,8 +234,12 @@ __device__ __forceinline__ void bw_scatter(const Args& a, const BwTable& tb, con
   const int64_t img = (int64_t)b * 3 * a.Hp * a.Wp * 128 + c4 * 16;
   const char* pbase = reinterpret_cast<const char*>(a.planes) + img;
   char* gbase = reinterpret_cast<char*>(a.g_planes) + img;
-#pragma unroll 1
-  for (int it = 0; it < 4; ++it) {
+#ifndef NFI_BW_SCAT_UNROLL
+#define NFI_BW_SCAT_UNROLL 1
+#endif
+  constexpr int kScatUnroll = NFI_BW_SCAT_UNROLL;
+#pragma unroll (kScatUnroll)
+  for (int it = 0; it < kBwRows / 4; ++it) {
     const int sl = it * 4 + (lane >> 3);
     const int s = bw_row(w, sl);
     const float keep = tb.keep[s];
@@ -359,11 +367,11 @@ field_bwd_ws_kernel(const Args a) {
   if (warp < kBwPS) {
     // ------------------------------------------------------------------ gather / scatter
     const int w = warp;
-    const int row = bw_row(w, lane & 15);
+    const int row = bw_row(w, lane & (kBwRows - 1));
     const uint32_t lane_off = (uint32_t)((w & 3) * 32) << 16;
     uint32_t df_ph[2] = {0, 0};
     BwIn& in = sm.in[w];
-    if (lane < 16 && total > 0) bw_prefetch<PTS, MODE>(a, in, 0, tm.tile(0), row, lane, per_image);
+    if (lane < kBwRows && total > 0) bw_prefetch<PTS, MODE>(a, in, 0, tm.tile(0), row, lane, per_image);
     for (uint32_t it = 0; it < total + kBwLag; ++it) {
       if (it < total) {
         const uint32_t m = it % kBwNM, c = it & 1;
@@ -374,12 +382,12 @@ field_bwd_ws_kernel(const Args a) {
         if (w == 0 && lane == 0) NFI_BTRACE(0, it, 0);
         bool act = false;
         cp_async_wait_all();
-        if (lane < 16) act = bw_phase1<PTS, MODE>(a, tb, mt, in, b, t, row, lane, per_image);
+        if (lane < kBwRows) act = bw_phase1<PTS, MODE>(a, tb, mt, in, b, t, row, lane, per_image);
         const unsigned wany = __any_sync(0xffffffffu, act);
         if (lane == 0) mt.flag[w] = wany ? 1 : 0;
         __syncwarp();
         if (lane == 0) nfi_tc::mbar_arrive(&sm.meta_full[m]);
-        if (lane < 16 && it + 1 < total) {            // inputs of the next tile arrive during gather + scatter
+        if (lane < kBwRows && it + 1 < total) {            // inputs of the next tile arrive during gather + scatter
           const uint32_t n = it + 1;
           bw_prefetch<PTS, MODE>(a, in, (int)(n / (uint32_t)ntile), tm.tile((int)(n % (uint32_t)ntile)), row, lane, per_image);
         }
@@ -409,8 +417,8 @@ field_bwd_ws_kernel(const Args a) {
           nfi_tc::tmem_ld16(tl + 16, v1);
           nfi_tc::tmem_ld_wait();
           __syncwarp();                                   // the previous tile's scatter has read the scratch
-          if ((lane >> 4) == (w >> 2)) {
-            float* dst = &sm.df[w][(lane & 15) * kBwDfLd];
+          if (lane / kBwRows == (w >> 2)) {
+            float* dst = &sm.df[w][(lane % kBwRows) * kBwDfLd];
 #pragma unroll
             for (int q = 0; q < 4; ++q) {
               *reinterpret_cast<float4*>(dst + 4 * q) = make_float4(v0[4 * q], v0[4 * q + 1], v0[4 * q + 2], v0[4 * q + 3]);

@@ -105,6 +105,9 @@ __device__ __forceinline__ uint32_t mbar_test(uint64_t* bar, uint32_t parity) {
 __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
   uint32_t spins = 0;
   while (!mbar_try_wait(bar, parity)) {
+#ifdef NFI_WAIT_SLEEP
+    __nanosleep(NFI_WAIT_SLEEP);
+#endif
     if (++spins > (1u << 24)) __trap();
   }
 }

@@ -68,7 +68,16 @@ def ray_bundle(H, W, focal, cam2world, bbox=None, center=None, normalize=False):
 # ---------------------------------------------------------------------------------------------
 # A2  near / far   lib/nerf_utils.py:227-275 (always under no_grad in the reference, run.py:197)
 # ---------------------------------------------------------------------------------------------
+_NO_HIT_MSG = ("compute_near_far_planes: no ray intersects the scene box "
+               "(min(): expected a non-empty tensor)")
+_PENDING_HITS = []        # device hit counters of deferred checks (read back in one copy)
+
+
 def near_far(origins, dirs, scene_range, check_hits=True):
+    """check_hits: True -- raise right away like the reference (one host sync, nerf_utils.py:260);
+    "defer" -- keep the device counter; `raise_if_no_hits()` reads all pending counters back in one
+    copy at the caller's next synchronisation point (pipelined callers: a device->host copy on the
+    compute stream would queue behind the bulk output copies on the copy engine); False -- no check."""
     o = f32c(origins.detach())
     d = f32c(dirs.detach())
     shape = o.shape[:-1]
@@ -77,13 +86,28 @@ def near_far(origins, dirs, scene_range, check_hits=True):
     far = _empty(o, *shape)
     ws = _empty(o, NEARFAR_WS_BYTES, dtype=torch.uint8)
     call("nfi_near_far", o, ptr(o), ptr(d), R, float(scene_range), ptr(near), ptr(far), ptr(ws))
-    if check_hits:
+    if check_hits == "defer":
+        _PENDING_HITS.append(ws[:4].view(torch.int32))
+    elif check_hits:
         hits = int(ws[:4].view(torch.int32).item())
         if hits == 0:
             # the reference raises from near_plane[mask].min() on an empty tensor (nerf_utils.py:260)
-            raise RuntimeError("compute_near_far_planes: no ray intersects the scene box "
-                               "(min(): expected a non-empty tensor)")
+            raise RuntimeError(_NO_HIT_MSG)
     return near, far
+
+
+def raise_if_no_hits():
+    """Resolve the deferred checks of near_far(check_hits="defer")."""
+    if not _PENDING_HITS:
+        return
+    pending = list(_PENDING_HITS)
+    del _PENDING_HITS[:]
+    by_dev = {}
+    for t in pending:
+        by_dev.setdefault(t.device, []).append(t)
+    for ts in by_dev.values():
+        if int(torch.cat(ts).min().item()) == 0:
+            raise RuntimeError(_NO_HIT_MSG)
 
 
 # ---------------------------------------------------------------------------------------------

@@ -22,7 +22,7 @@ def render_planes(planes, palette, field: Field, height: int, width: int, tform_
                   focal_length=None, center=None, bbox=None, depth_samples_per_ray: int = 64,
                   randomize: bool = True, white_background: bool = False, fine_sampling: bool = True,
                   force_no_cam_grad: bool = False, zbuffer_depth: bool = False,
-                  planes_layout: str = "nchw", u_strat=None, u_pdf=None, check_hits: bool = True,
+                  planes_layout: str = "nchw", u_strat=None, u_pdf=None, check_hits=True,
                   return_aux: bool = False):
     """Render `B` images.  planes: [B,96,Hp,Wp] or [B,3,32,Hp,Wp] (layout 'nchw', the StyleGAN2
     output of models/generator.py:475-477) or [B,3,Hp,Wp,32] ('cl').  palette: attention values
