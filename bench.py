@@ -74,6 +74,9 @@ class ClockSampler(threading.Thread):
                 "reasons": reasons, "samples": len(sm)}
 
 
+NCU_BWD_DRAM_BYTES = 1150829000 + 569507000
+
+
 def make_inputs(B, H, W, S, seed_shift=0):
     """Synthetic config-2 inputs on the CPU: smooth planes, calibrated decoder,
     random object-centred perspective poses, l1 target."""
@@ -226,7 +229,11 @@ def run_ours(args):
         "gpu_launches": launches,
         "clocks": clocks,
         "roofline": {"bound": "hbm", "kernel": "field_bwd_ws_kernel", "achieved": ach, "peak": pk["hbm_gbs"],
-                     "unit": "GB/s", "frac": (ach / pk["hbm_gbs"]) if ach else None, "traffic": None,
+                     "unit": "GB/s", "frac": (ach / pk["hbm_gbs"]) if ach else None,
+                     # dram__bytes_read.sum + dram__bytes_write.sum of one launch at this config, from the
+                     # committed ncu --set full capture (profiles/r01d_field_ws_ncu_full_summary.txt)
+                     "traffic": NCU_BWD_DRAM_BYTES if (B == 16 and H == 128) else None,
+                     "traffic_source": "profiles/r01d_field_ws_ncu_full_summary.txt",
                      "peak_source": pk_src, "algorithmic_bytes_per_launch": a_bytes,
                      "launch_ms": bwd_ms, "launches_timed": len(bwd),
                      "share_of_step": (sum(bwd) / args.steps) / ms_step if ms_step else None,
