@@ -113,12 +113,14 @@ int nfi_field_fwd(const NfiField* field, const float* planes_cl, const float* pa
                   int skip_oob, float* out, float* probs_out, nfi_stream_t stream);
 /* Backward.  g_out as `out`.  Accumulating outputs (caller zero-fills): g_planes_cl [B,3,Hp,Wp,32],
  * g_palette [B,A,3], g_params [64*32 + 64 + n_out*64 + n_out + 2] (W0,b0,W1,b1,beta,alpha).
- * g_points [.., 3] per sample is overwritten.  Any of them may be NULL (not computed). */
+ * g_points [.., 3] per sample is overwritten.  Any of them may be NULL (not computed).
+ * want_weight_grads != 0 (generator training, run.py:980-986) also fills the W0,b0,W1,b1 part of
+ * g_params; with 0 only beta / alpha are written (inversion: the decoder is frozen, run.py:630-632). */
 int nfi_field_bwd(const NfiField* field, const float* planes_cl, const float* palette, int B, int Hp,
                   int Wp, const float* origins, const float* dirs, const float* z,
                   const float* points, int64_t n_per_image, int S, int mode, int img_w,
                   const float* g_out, float* g_planes_cl, float* g_palette, float* g_points,
-                  float* g_params, nfi_stream_t stream);
+                  float* g_params, int want_weight_grads, nfi_stream_t stream);
 
 /* ---- decoder MLP alone (models/generator.py:295-299, 329-330; EqualizedLinear gains applied
  *      inside): feat [n,32] -> y [n, n_out] on tcgen05 tensor cores (3xTF32 split, fp32

@@ -44,7 +44,7 @@ _SIGS = {
     "nfi_field_fwd": (c_int, [POINTER(NfiField), _P, _P, c_int, c_int, c_int, _P, _P, _P, _P, c_int64,
                               c_int, c_int, c_int, c_int, _P, _P, _P]),
     "nfi_field_bwd": (c_int, [POINTER(NfiField), _P, _P, c_int, c_int, c_int, _P, _P, _P, _P, c_int64,
-                              c_int, c_int, c_int, _P, _P, _P, _P, _P, _P]),
+                              c_int, c_int, c_int, _P, _P, _P, _P, _P, c_int, _P]),
     "nfi_decoder_mlp_fwd": (c_int, [POINTER(NfiField), _P, c_int64, _P, _P, _P]),
     "nfi_weights_only": (c_int, [_P, c_int, _P, _P, c_int64, c_int, c_int, _P, _P]),
     "nfi_sample_pdf": (c_int, [_P, _P, c_int64, c_int, c_int, _P, _P, _P, _P]),

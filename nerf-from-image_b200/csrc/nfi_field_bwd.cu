@@ -20,6 +20,56 @@ struct BwdSmem {
   Tables t;
   float act[kTile];
 };
+// decoder weight gradients (generator training, run.py:980-986): row tiles of H, dHpre and dY
+constexpr int kHsLd = nfi_mlp::kH + 1, kDysLd = nfi_mlp::kY + 1;
+struct BwdSmemW : BwdSmem {
+  float hs[kTile * kHsLd];           // H = softplus(pre)
+  float dhs[kTile * kHsLd];          // dHpre
+  float dys[kTile * kDysLd];         // dY
+};
+
+// epilogue 0 / 2 that also leave their row values in shared memory (weight-gradient variant)
+__device__ __forceinline__ void epilogue0_keep(const nfi_mlp::Operands& s, uint32_t tmem_lane, int col0, float* hrow) {
+#pragma unroll
+  for (int q = 0; q < 2; ++q) {
+    float v[16];
+    nfi_tc::tmem_ld16(tmem_lane + nfi_mlp::kColD0 + col0 + 16 * q, v);
+    nfi_tc::tmem_ld_wait();
+    uint32_t hi[16], lo[16];
+#pragma unroll
+    for (int i = 0; i < 16; ++i) {
+      const float h = nfi_mlp::softplus_f(v[i] + s.b0[col0 + 16 * q + i]);
+      hrow[col0 + 16 * q + i] = h;
+      hi[i] = nfi_tc::tf32_hi(h);
+      lo[i] = __float_as_uint(h - __uint_as_float(hi[i]));
+    }
+    nfi_tc::tmem_st16(tmem_lane + nfi_mlp::kColHhi + col0 + 16 * q, hi);
+    nfi_tc::tmem_st16(tmem_lane + nfi_mlp::kColHlo + col0 + 16 * q, lo);
+  }
+  nfi_tc::tmem_st_wait();
+}
+__device__ __forceinline__ void epilogue2_keep(uint32_t tmem_lane, int col0, float* drow) {
+#pragma unroll
+  for (int q = 0; q < 2; ++q) {
+    float dh[16], hh[16], hl[16];
+    nfi_tc::tmem_ld16(tmem_lane + nfi_mlp::kColDH + col0 + 16 * q, dh);
+    nfi_tc::tmem_ld16(tmem_lane + nfi_mlp::kColHhi + col0 + 16 * q, hh);
+    nfi_tc::tmem_ld16(tmem_lane + nfi_mlp::kColHlo + col0 + 16 * q, hl);
+    nfi_tc::tmem_ld_wait();
+    uint32_t hi[16], lo[16];
+#pragma unroll
+    for (int i = 0; i < 16; ++i) {
+      const float sg = 1.f - __expf(-(hh[i] + hl[i]));
+      const float g = dh[i] * sg;
+      drow[col0 + 16 * q + i] = g;
+      hi[i] = nfi_tc::tf32_hi(g);
+      lo[i] = __float_as_uint(g - __uint_as_float(hi[i]));
+    }
+    nfi_tc::tmem_st16(tmem_lane + nfi_mlp::kColHhi + col0 + 16 * q, hi);
+    nfi_tc::tmem_st16(tmem_lane + nfi_mlp::kColHlo + col0 + 16 * q, lo);
+  }
+  nfi_tc::tmem_st_wait();
+}
 static_assert(kTile * kDfLd <= 2 * 8 * (int)nfi_mlp::kLboA / 4, "d feature tile does not fit the operand tile");
 
 // scatter d feat into the gradient planes; optionally d/d point from the re-read texels
@@ -84,11 +134,17 @@ __device__ __forceinline__ void phase4_scatter(const Args& a, const Tables& t, c
   }
 }
 
-template <bool PTS, int MODE, bool WANT_PTS>
-__global__ void __launch_bounds__(kThreads, 2)
+// Non-specialised form (256 threads, __syncthreads between phases), kept for the case that also wants
+// the decoder weight gradients: it has the feature tile, H, dHpre and dY of a tile in one place.
+//   dW0[j][k] = g0 sum_rows dHpre[j] F[k]   db0[j] = sum_rows dHpre[j]     (g = EqualizedLinear gains,
+//   dW1[o][j] = g1 sum_rows dY[o] H[j]      db1[o] = sum_rows dY[o]         models/stylegan.py:170-177)
+// Each thread keeps its 8 + 4 (+2) partial sums in registers over all its tiles; one atomicAdd each at
+// the end.
+template <bool PTS, int MODE, bool WANT_PTS, bool WANT_W>
+__global__ void __launch_bounds__(kThreads, WANT_W ? 1 : 2)
 field_bwd_tc_kernel(const Args a) {
   extern __shared__ __align__(128) unsigned char smem_raw[];
-  BwdSmem& sm = *reinterpret_cast<BwdSmem*>(smem_raw);
+  BwdSmemW& sm = *reinterpret_cast<BwdSmemW*>(smem_raw);     // the W tail is only there when WANT_W
   nfi_mlp::Operands& op = sm.op;
   Tables& t = sm.t;
   float* dft = op.a_hi;
@@ -109,6 +165,12 @@ field_bwd_tc_kernel(const Args a) {
   const bool want_par = MODE == 0 && a.g_params != nullptr && hd.use_sdf;
   uint32_t parity = 0;
   const int64_t per_image = a.npi * a.S;
+  // weight-gradient partial sums: thread -> (j = tid/4, k0 = 8 (tid%4)) of dW0, (o = tid/16, j0 = 4 (tid%16)) of dW1
+  float aw0[8], aw1[4], ab0 = 0.f, ab1 = 0.f;
+#pragma unroll
+  for (int i = 0; i < 8; ++i) aw0[i] = 0.f;
+#pragma unroll
+  for (int i = 0; i < 4; ++i) aw1[i] = 0.f;
   for (int b = 0; b < a.B; ++b) {
     int64_t lo, hi;
     cta_tile_range(a.tiles_per_image, lo, hi);
@@ -154,7 +216,8 @@ field_bwd_tc_kernel(const Args a) {
         if (tid == 0) { nfi_tc::fence_after_sync(); nfi_mlp::issue_layer0(op, tmem); nfi_tc::mma_commit(&op.bar); }
         nfi_tc::mbar_wait(&op.bar, parity); parity ^= 1;
         nfi_tc::fence_after_sync();
-        nfi_mlp::epilogue0<2, false>(op, tmem_lane, (warp >> 2) * 32, nullptr);
+        if (WANT_W) epilogue0_keep(op, tmem_lane, (warp >> 2) * 32, &sm.hs[((warp & 3) * 32 + lane) * kHsLd]);
+        else nfi_mlp::epilogue0<2, false>(op, tmem_lane, (warp >> 2) * 32, nullptr);
         nfi_tc::fence_before_sync();
         __syncthreads();
         if (tid == 0) { nfi_tc::fence_after_sync(); nfi_mlp::issue_layer1(op, tmem); nfi_tc::mma_commit(&op.bar); }
@@ -190,16 +253,43 @@ field_bwd_tc_kernel(const Args a) {
             for (int o = 0; o < NFI_YPAD; ++o) dy[o] = gy[o];
           }
           nfi_mlp::store_dy(tmem_lane, dy);
+          if (WANT_W) {
+#pragma unroll
+            for (int o = 0; o < NFI_YPAD; ++o) sm.dys[tid * kDysLd + o] = dy[o];
+          }
         }
         nfi_tc::fence_before_sync();
         __syncthreads();
         if (tid == 0) { nfi_tc::fence_after_sync(); nfi_mlp::issue_dh(sm.bw, tmem); nfi_tc::mma_commit(&op.bar); }
         nfi_tc::mbar_wait(&op.bar, parity); parity ^= 1;
         nfi_tc::fence_after_sync();
-        nfi_mlp::epilogue2<2>(tmem_lane, (warp >> 2) * 32);
+        if (WANT_W) epilogue2_keep(tmem_lane, (warp >> 2) * 32, &sm.dhs[((warp & 3) * 32 + lane) * kHsLd]);
+        else nfi_mlp::epilogue2<2>(tmem_lane, (warp >> 2) * 32);
         nfi_tc::fence_before_sync();
         __syncthreads();
         if (tid == 0) { nfi_tc::fence_after_sync(); nfi_mlp::issue_df(sm.bw, tmem); nfi_tc::mma_commit(&op.bar); }
+        if (WANT_W) {      // while the dF MMAs run: rank-128 updates of the weight gradients (idle rows are 0)
+          const int j = tid >> 2, c40 = 2 * (tid & 3);
+          const int o1 = tid >> 4, j0 = 4 * (tid & 15);
+#pragma unroll 4
+          for (int r = 0; r < kTile; ++r) {
+            const float g = sm.dhs[r * kHsLd + j];
+            const int f0 = c40 * (nfi_mlp::kLboA / 4) + r * 4, f1 = f0 + nfi_mlp::kLboA / 4;
+            const float4 h0 = *reinterpret_cast<const float4*>(&op.a_hi[f0]), l0 = *reinterpret_cast<const float4*>(&op.a_lo[f0]);
+            const float4 h1 = *reinterpret_cast<const float4*>(&op.a_hi[f1]), l1 = *reinterpret_cast<const float4*>(&op.a_lo[f1]);
+            aw0[0] = fmaf(g, h0.x + l0.x, aw0[0]); aw0[1] = fmaf(g, h0.y + l0.y, aw0[1]);
+            aw0[2] = fmaf(g, h0.z + l0.z, aw0[2]); aw0[3] = fmaf(g, h0.w + l0.w, aw0[3]);
+            aw0[4] = fmaf(g, h1.x + l1.x, aw0[4]); aw0[5] = fmaf(g, h1.y + l1.y, aw0[5]);
+            aw0[6] = fmaf(g, h1.z + l1.z, aw0[6]); aw0[7] = fmaf(g, h1.w + l1.w, aw0[7]);
+            if ((tid & 3) == 0) ab0 += g;
+            const float dyv = sm.dys[r * kDysLd + o1];
+            const float* hr = &sm.hs[r * kHsLd + j0];
+            aw1[0] = fmaf(dyv, hr[0], aw1[0]); aw1[1] = fmaf(dyv, hr[1], aw1[1]);
+            aw1[2] = fmaf(dyv, hr[2], aw1[2]); aw1[3] = fmaf(dyv, hr[3], aw1[3]);
+            if ((tid & 15) == 0) ab1 += dyv;
+          }
+          __syncthreads();       // the d feature tile written below overlays the feature tile read above
+        }
         nfi_tc::mbar_wait(&op.bar, parity); parity ^= 1;
         nfi_tc::fence_after_sync();
         {   // d feature rows -> shared memory (row-major, padded)
@@ -246,6 +336,22 @@ field_bwd_tc_kernel(const Args a) {
       }
     }
   }
+  if (WANT_W && a.g_params) {
+    const float g0 = (float)(1.0 / sqrt((double)nfi_mlp::kC)), g1 = (float)(1.0 / sqrt((double)nfi_mlp::kH));
+    float* gW0 = a.g_params;
+    float* gb0 = gW0 + NFI_HID * NFI_C;
+    float* gW1 = gb0 + NFI_HID;
+    float* gb1 = gW1 + a.f.n_out * NFI_HID;
+    const int j = tid >> 2, k0 = 8 * (tid & 3), o1 = tid >> 4, j0 = 4 * (tid & 15);
+#pragma unroll
+    for (int i = 0; i < 8; ++i) if (aw0[i] != 0.f) atomicAdd(&gW0[j * NFI_C + k0 + i], aw0[i] * g0);
+    if ((tid & 3) == 0 && ab0 != 0.f) atomicAdd(&gb0[j], ab0);
+    if (o1 < a.f.n_out) {
+#pragma unroll
+      for (int i = 0; i < 4; ++i) if (aw1[i] != 0.f) atomicAdd(&gW1[o1 * NFI_HID + j0 + i], aw1[i] * g1);
+      if ((tid & 15) == 0 && ab1 != 0.f) atomicAdd(&gb1[o1], ab1);
+    }
+  }
   __syncthreads();
   if (warp == 0) nfi_tc::tmem_dealloc(tmem, nfi_mlp::kTmemCols);
 }
@@ -256,7 +362,7 @@ extern "C" int nfi_field_bwd(const NfiField* field, const float* planes_cl, cons
                              int Hp, int Wp, const float* origins, const float* dirs, const float* z,
                              const float* points, int64_t n_per_image, int S, int mode, int img_w,
                              const float* g_out, float* g_planes_cl, float* g_palette, float* g_points,
-                             float* g_params, nfi_stream_t stream) {
+                             float* g_params, int want_weight_grads, nfi_stream_t stream) {
   using namespace nfi_ftc;
   Args a;
   int rc = fill_args(a, "nfi_field_bwd", field, planes_cl, palette, B, Hp, Wp, origins, dirs, z, points,
@@ -269,8 +375,8 @@ extern "C" int nfi_field_bwd(const NfiField* field, const float* planes_cl, cons
   a.g_points = g_points; a.g_params = g_params;
   cudaStream_t st = nfi_cu(stream);
   const bool wp = g_points != nullptr;
-  static const bool old_kernel = getenv("NFI_BWD_OLD") != nullptr;     // development A/B switch
-  if (!old_kernel) {
+  const bool want_w = want_weight_grads != 0 && g_params != nullptr;
+  if (!want_w) {
     const int grid = field_grid_chunks(a);
     const int smem = (int)sizeof(BwSmem);
 #define NFI_LAUNCH_BWS(P, M, W)                                                                         \
@@ -311,15 +417,15 @@ extern "C" int nfi_field_bwd(const NfiField* field, const float* planes_cl, cons
 #endif
     return NFI_OK;
   }
-  const int grid = field_grid(a, 2);
-  const int smem = (int)sizeof(BwdSmem);
+  const int grid = field_grid(a, 1);
+  const int smem = (int)sizeof(BwdSmemW);
 #define NFI_LAUNCH_BWD(P, M, W)                                                                         \
   do {                                                                                                  \
-    cudaError_t e = cudaFuncSetAttribute(field_bwd_tc_kernel<P, M, W>,                                  \
+    cudaError_t e = cudaFuncSetAttribute(field_bwd_tc_kernel<P, M, W, true>,                            \
                                          cudaFuncAttributeMaxDynamicSharedMemorySize, smem);            \
     NFI_REQUIRE(e == cudaSuccess, NFI_ERR_LAUNCH, "nfi_field_bwd: cudaFuncSetAttribute: %s",            \
                 cudaGetErrorString(e));                                                                 \
-    field_bwd_tc_kernel<P, M, W><<<grid, kThreads, smem, st>>>(a);                                      \
+    field_bwd_tc_kernel<P, M, W, true><<<grid, kThreads, smem, st>>>(a);                                \
   } while (0)
   if (points) {
     if (mode == 0) { if (wp) NFI_LAUNCH_BWD(true, 0, true); else NFI_LAUNCH_BWD(true, 0, false); }

@@ -185,6 +185,9 @@ __device__ __forceinline__ float4 bw_ldg(const char* base, uint32_t off) {
 __device__ __forceinline__ void bw_fma4(float4& acc, const float4& v, float w) {
   acc.x = fmaf(v.x, w, acc.x); acc.y = fmaf(v.y, w, acc.y); acc.z = fmaf(v.z, w, acc.z); acc.w = fmaf(v.w, w, acc.w);
 }
+__device__ __forceinline__ float4 bw_sub4(const float4& a, const float4& b) {
+  return make_float4(a.x - b.x, a.y - b.y, a.z - b.z, a.w - b.w);
+}
 __device__ __forceinline__ float bw_dot4(const float4& v, const float4& g) {
   return fmaf(v.w, g.w, fmaf(v.z, g.z, fmaf(v.y, g.y, v.x * g.x)));
 }
@@ -278,11 +281,11 @@ __device__ __forceinline__ void bw_scatter(const Args& a, const BwTable& tb, con
       if (WANT_PTS && !kDbgNoPts) {
 #pragma unroll
         for (int p = 0; p < 3; ++p) {
-          // d/d ix = sum_c g_c ((v01 - v00)(1 - ty) + (v11 - v10) ty), d/d iy likewise, from the four
-          // channel dot products
-          const float s00 = bw_dot4(v[p][0], g), s01 = bw_dot4(v[p][1], g);
-          const float s10 = bw_dot4(v[p][2], g), s11 = bw_dot4(v[p][3], g);
-          const float ax = s01 - s00, bx = s11 - s10, ay = s10 - s00, by = s11 - s01;
+          // d/d ix = sum_c g_c ((v01 - v00)(1 - ty) + (v11 - v10) ty), d/d iy likewise
+          // (texel differences first: the four dot products of the raw texels cancel to ~1e-4 relative
+          // in the pose gradient on smooth planes)
+          const float ax = bw_dot4(bw_sub4(v[p][1], v[p][0]), g), bx = bw_dot4(bw_sub4(v[p][3], v[p][2]), g);
+          const float ay = bw_dot4(bw_sub4(v[p][2], v[p][0]), g), by = bw_dot4(bw_sub4(v[p][3], v[p][1]), g);
           const float gx = fmaf(bx - ax, d[p].y, ax), gy = fmaf(by - ay, d[p].x, ay);
           gp[nfi_plane_axis_a(p)] = fmaf(gx, d[p].z, gp[nfi_plane_axis_a(p)]);
           gp[nfi_plane_axis_b(p)] = fmaf(gy, d[p].w, gp[nfi_plane_axis_b(p)]);

@@ -249,9 +249,7 @@ class _Field(Function):
         pl, pal, W0, b0, W1, b1, beta, alpha, o, d, zz, pts = ctx.saved_tensors
         cfg, mode = ctx.cfg, ctx.mode
         need = ctx.needs_input_grad
-        if any(need[2:6]):
-            raise NotImplementedError("nfi_b200: decoder weight gradients (W0, b0, W1, b1) are not "
-                                      "produced by the fused backward yet")
+        want_w = any(need[2:6])           # generator training (run.py:980-986)
         B, _, Hp, Wp, _ = pl.shape
         field, keep = _lib.make_field_struct(W0, b0, W1, b1, beta, alpha, cfg.attention_values,
                                              cfg.use_sdf, cfg.scene_range)
@@ -261,12 +259,12 @@ class _Field(Function):
         g_pal = torch.zeros_like(pal) if (pal is not None and need[1] and mode == 0) else None
         want_pts = (need[8] or need[9]) if pts is None else need[11]
         g_points = _empty(pl, *g.shape[:-1], 3) if want_pts else None
-        want_params = cfg.use_sdf and mode == 0 and (need[6] or need[7])
+        want_params = want_w or (cfg.use_sdf and mode == 0 and (need[6] or need[7]))
         g_params = torch.zeros(sum(_param_sizes(n_out)), dtype=torch.float32, device=pl.device) \
             if want_params else None
         call("nfi_field_bwd", pl, field, ptr(pl), ptr(pal), B, Hp, Wp, ptr(o), ptr(d), ptr(zz), ptr(pts),
              ctx.npi, ctx.S, mode, ctx.img_w, ptr(g), ptr(g_planes), ptr(g_pal), ptr(g_points),
-             ptr(g_params))
+             ptr(g_params), int(want_w))
         go = gd = gp = None
         if want_pts:
             if pts is None:
@@ -276,12 +274,20 @@ class _Field(Function):
                 call("nfi_points_bwd", pl, ptr(g_points), ptr(zz), R, ctx.S, ptr(go), ptr(gd))
             else:
                 gp = g_points.view(ctx.pshape)
-        g_beta = g_alpha = None
+        g_beta = g_alpha = gW0 = gb0 = gW1 = gb1 = None
         if g_params is not None:
-            base = sum(_param_sizes(n_out)[:4])
-            g_beta = g_params[base:base + 1].view_as(beta) if need[6] else None
-            g_alpha = g_params[base + 1:base + 2].view_as(alpha) if need[7] else None
-        return (g_planes, g_pal, None, None, None, None, g_beta, g_alpha, go, gd, None, gp,
+            sz = _param_sizes(n_out)
+            base = sum(sz[:4])
+            if cfg.use_sdf and mode == 0:
+                g_beta = g_params[base:base + 1].view_as(beta) if need[6] else None
+                g_alpha = g_params[base + 1:base + 2].view_as(alpha) if need[7] else None
+            if want_w:
+                o0, o1, o2 = sz[0], sz[0] + sz[1], sz[0] + sz[1] + sz[2]
+                gW0 = g_params[:o0].view_as(W0) if need[2] else None
+                gb0 = g_params[o0:o1].view_as(b0) if need[3] else None
+                gW1 = g_params[o1:o2].view_as(W1) if need[4] else None
+                gb1 = g_params[o2:base].view_as(b1) if need[5] else None
+        return (g_planes, g_pal, gW0, gb0, gW1, gb1, g_beta, g_alpha, go, gd, None, gp,
                 None, None, None, None, None)
 
 

@@ -210,6 +210,13 @@ def test_decoder_and_heads(nfi, name, A, use_sdf):
     gd = torch.autograd.grad((y * cu(g["gy"])).sum(), [planes, pts])
     assert rel_err(gd[0].cpu(), g["dy_planes"]) < TOL
     assert rel_err(gd[1].cpu(), g["dy_pts"]) < TOL
+    # decoder weight gradients (generator training, run.py:980-986)
+    wl = [t.clone().requires_grad_() for t in (fld.W0, fld.b0, fld.W1, fld.b1)]
+    yw, _ = nfi.ops.field_on_points(pcl, None, *wl, None, None, pts / 1.4, cfg_raw, mode=1)
+    gw = torch.autograd.grad((yw * cu(g["gy"])).sum(), [planes] + wl)
+    assert rel_err(gw[0].cpu(), g["dy_planes"]) < TOL
+    for a, k in zip(gw[1:], ("dy_W0", "dy_b0", "dy_W1", "dy_b1")):
+        assert rel_err(a.cpu(), g[k]) < TOL, k
     # heads
     if use_sdf:     # beta / alpha are trainable in G training (generator.py:397-399)
         fld.beta, fld.alpha = fld.beta.clone().requires_grad_(), fld.alpha.clone().requires_grad_()
@@ -278,3 +285,87 @@ def test_decoder_mlp_tensor_cores(nfi, n):
     y, hp = nfi.ops.decoder_mlp(cu(feat), cu(W0), cu(b0), cu(W1), cu(b1), want_hidden=True)
     assert rel_err(hp.cpu(), hp_ref) < 5e-6
     assert rel_err(y.cpu(), y_ref) < 5e-6
+
+
+# ---------------------------------------------------------------- A11/A12 against the live oracle
+def _oracle_vs_cuda(nfi, B, H, W, S, res, perspective, train, white, no_cam, seed=0):
+    """One render forward + backward through the C ABI and through the CPU oracle on the same seeded
+    inputs; returns {name: relative error}.  train=True is the generator-training gradient set
+    (planes, attention values, W0, b0, W1, b1, beta, alpha; poses are data)."""
+    import nfi_oracle as O
+    from nfi_b200 import synth
+    planes = synth.make_planes(B, res=res, seed=1 + seed)
+    fd = synth.make_field(planes, seed=3 + seed)
+    pal = synth.make_palette(B, 10, seed=4 + seed)
+    cam, focal = synth.make_cameras(B, seed=2 + seed, perspective=perspective)
+    g = torch.Generator().manual_seed(99 + seed)
+    u_s = torch.rand(B, H, W, S, generator=g)
+    u_p = torch.rand(B * H * W, S, generator=g)
+    target = torch.rand(B, H, W, 3, generator=g) * 2 - 1
+    wkeys = ("W0", "b0", "W1", "b1", "beta", "alpha")
+
+    def run(dev):
+        lv = {"planes": planes, "palette": pal}
+        if not train and not no_cam:
+            lv["cam"] = cam
+            if perspective:
+                lv["focal"] = focal
+        if train:
+            lv.update({k: fd[k] for k in wkeys})
+        lv = {k: v.clone().to(dev).requires_grad_() for k, v in lv.items()}
+        w = {k: lv.get(k, fd[k].to(dev)) for k in wkeys}
+        c = lv.get("cam", cam.to(dev))
+        f = (lv.get("focal", focal.to(dev)) if perspective else None)
+        if dev == "cpu":
+            fp = O.FieldParams(w["W0"], w["b0"], w["W1"], w["b1"], 1.4, True, 10, w["beta"], w["alpha"])
+            out = O.render(lv["planes"].view(B, 3, 32, res, res), lv["palette"], fp, H, W, c, f, None, None, S,
+                           white, u_s, u_p, True, True, no_cam, return_aux=True)
+        else:
+            fld = nfi.dec.Field(*[w[k] for k in wkeys], 1.4, 10, True)
+            out = nfi.render.render_planes(lv["planes"], lv["palette"], fld, H, W, c, f, None, None, S,
+                                           randomize=True, white_background=white, force_no_cam_grad=no_cam,
+                                           u_strat=u_s.to(dev), u_pdf=u_p.to(dev), return_aux=True)
+        rgb, depth, mask = out[:3]
+        loss = (rgb - target.to(dev)).abs().mean() * B + 0.1 * mask.mean()
+        grads = torch.autograd.grad(loss, list(lv.values()))
+        res_ = {"rgb": rgb, "depth": depth, "mask": mask}
+        res_.update({"d_" + k: gr for k, gr in zip(lv, grads)})
+        return res_, out[3]["z_fine"].detach().cpu().reshape(-1)
+
+    (ref, zf_ref), (got, zf_got) = run("cpu"), run("cuda")
+    assert float(ref["mask"].detach().mean()) > 0.05, "vacuous fixture"
+    errs = {k: rel_err(got[k].detach().cpu(), ref[k].detach()) for k in ref}
+    # importance samples that moved by a whole bin between the two summation orders (SURVEY.md 7.3-3)
+    flips = int(((zf_got - zf_ref).abs() > 1e-4 * zf_ref.abs().clamp_min(1.0)).sum())
+    return errs, flips, zf_ref.numel()
+
+
+# Pose gradients (d_cam, d_focal) are sums over every sample of a piecewise-constant quantity: the
+# bilinear coordinate gradient jumps at texel boundaries.  Of the ~1e5 fine samples of an image a few
+# land within an ulp or two of a boundary (their depth comes out of the inverse CDF, which differs
+# by ulps between the CPU and the GPU exp), floor() puts them in different cells, and that one sample
+# moves the pose gradient of its ray by O(1) (tools/dev/cam_probe2.py shows the rays).  The committed
+# reference fixtures (test_render_golden) hold d_cam / d_focal to 1e-4; here, on fresh seeds, they get
+# the looser bound and everything else the contract tolerance.
+POSE_TOL = 5e-3
+
+
+def _check(errs, flips, n):
+    assert flips <= max(2, n // 100000), "too many importance-sample mismatches: %d of %d" % (flips, n)
+    for k, v in errs.items():
+        tol = POSE_TOL if k in ("d_cam", "d_focal") else TOL
+        assert v < tol, (k, v, flips)
+
+
+@pytest.mark.parametrize("B,HW,perspective,white,no_cam", [
+    (1, 32, True, False, False), (3, 32, True, True, False), (2, 32, False, False, False),
+    (2, 16, True, False, True), (1, 64, True, False, False)])
+def test_render_vs_oracle_sizes(nfi, B, HW, perspective, white, no_cam):
+    _check(*_oracle_vs_cuda(nfi, B, HW, HW, 64, 64, perspective, False, white, no_cam))
+
+
+def test_render_training_gradients_vs_oracle(nfi):
+    """Generator-training gradient set: decoder weights, beta, alpha, planes, attention values."""
+    errs, flips, n = _oracle_vs_cuda(nfi, 2, 32, 32, 64, 64, True, True, False, False, seed=5)
+    _check(errs, flips, n)
+    assert {"d_W0", "d_b0", "d_W1", "d_b1", "d_beta", "d_alpha"} <= set(errs)
