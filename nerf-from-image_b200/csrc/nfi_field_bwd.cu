@@ -59,7 +59,7 @@ __device__ __forceinline__ void epilogue2_keep(uint32_t tmem_lane, int col0, flo
     uint32_t hi[16], lo[16];
 #pragma unroll
     for (int i = 0; i < 16; ++i) {
-      const float sg = 1.f - __expf(-(hh[i] + hl[i]));
+      const float sg = 1.f - nfi_tc::ex2_ftz((hh[i] + hl[i]) * -1.4426950408889634f);
       const float g = dh[i] * sg;
       drow[col0 + 16 * q + i] = g;
       hi[i] = nfi_tc::tf32_hi(g);

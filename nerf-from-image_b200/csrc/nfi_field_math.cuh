@@ -7,7 +7,13 @@
 // exp on the MUFU pipe in kernels (ex2.approx: relative error ~2^-21, far inside the 1e-4 contract);
 // the host emulation build (tests/hostcheck) uses libm.
 #if defined(__CUDA_ARCH__)
-#define NFI_EXPF(x) __expf(x)
+// flush-to-zero form: no denormal fix-up instructions around the MUFU op
+__device__ __forceinline__ float nfi_exp_fast(float x) {
+  float y;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x * 1.4426950408889634f));
+  return y;
+}
+#define NFI_EXPF(x) nfi_exp_fast(x)
 #else
 #define NFI_EXPF(x) expf(x)
 #endif

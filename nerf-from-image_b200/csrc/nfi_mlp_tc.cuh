@@ -105,8 +105,8 @@ __device__ __forceinline__ void issue_layer1(const Operands& s, uint32_t tmem) {
 // MUFU pipe (ex2.approx / lg2.approx): absolute error < 3e-7, and for x > 20 the correction term
 // is below 2.1e-9, i.e. the reference's linear branch within fp32 resolution.
 __device__ __forceinline__ float softplus_f(float x) {
-  const float t = __expf(-fabsf(x));
-  return fmaxf(x, 0.f) + __logf(1.f + t);
+  const float t = nfi_tc::ex2_ftz(fabsf(x) * -1.4426950408889634f);
+  return fmaf(nfi_tc::lg2_ftz(1.f + t), 0.6931471805599453f, fmaxf(x, 0.f));
 }
 
 // Epilogue 0 for 16*NQ hidden columns starting at col0 of this thread's TMEM lane:
@@ -337,7 +337,7 @@ __device__ __forceinline__ void epilogue2(uint32_t tmem_lane, int col0) {
     uint32_t hi[16], lo[16];
 #pragma unroll
     for (int i = 0; i < 16; ++i) {
-      const float sg = 1.f - __expf(-(hh[i] + hl[i]));
+      const float sg = 1.f - nfi_tc::ex2_ftz((hh[i] + hl[i]) * -1.4426950408889634f);
       const float g = dh[i] * sg;
       hi[i] = nfi_tc::tf32_hi(g);
       lo[i] = __float_as_uint(g - __uint_as_float(hi[i]));

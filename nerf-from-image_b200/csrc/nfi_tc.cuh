@@ -161,6 +161,20 @@ __device__ __forceinline__ void tmem_st16(uint32_t taddr, const uint32_t (&r)[16
 }
 __device__ __forceinline__ void tmem_st_wait() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
 
+// ---- MUFU transcendentals, flush-to-zero forms: no denormal range fix-up around the MUFU op (exp of a
+// very negative argument is 0, which is what every use here wants) ----------------------------------
+__device__ __forceinline__ float ex2_ftz(float x) {
+  float y;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+__device__ __forceinline__ float lg2_ftz(float x) {
+  float y;
+  asm("lg2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+__device__ __forceinline__ float exp_fast(float x) { return ex2_ftz(x * 1.4426950408889634f); }
+
 // ---- 3xTF32 split -------------------------------------------------------------------------------
 __device__ __forceinline__ uint32_t tf32_hi(float x) { return __float_as_uint(x) & 0xFFFFE000u; }
 __device__ __forceinline__ float tf32_lo(float x) { return x - __uint_as_float(tf32_hi(x)); }   // exact
