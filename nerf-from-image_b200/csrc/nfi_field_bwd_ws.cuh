@@ -34,8 +34,15 @@ constexpr int kBwPS = NFI_BW_PS;         // gather / scatter warps (8 or 16)
 constexpr int kBwRows = kTile / kBwPS;   // rows of a tile owned by one of them
 constexpr int kBwE = 8;                  // epilogue warps (2 groups of 4)
 constexpr int kBwThreads = (kBwPS + kBwE + 1) * 32;     // 544
-constexpr int kBwNT = 3;                 // table ring: tiles it, it-1, it-2
-constexpr int kBwNM = 8;                 // meta ring
+#ifndef NFI_BW_EROWS
+#define NFI_BW_EROWS 8
+#endif
+#ifndef NFI_BW_RING
+#define NFI_BW_RING 3
+#endif
+constexpr int kBwNT = NFI_BW_RING;       // table ring: a slot is free once the tile's epilogue group has scattered it
+constexpr int kBwER = NFI_BW_EROWS;      // rows of dF an epilogue warp stages at a time for its atomics
+constexpr int kBwNM = 8;               // ring of tables + meta: a slot is free once the epilogue group has scattered its tile
 constexpr int kBwLag = 2;                // scatter runs this many tiles behind the gather
 constexpr int kBwDfLd = 36;              // dF scratch row stride (floats)
 constexpr int kBwRed = 32;               // per-image scalar gradients reduced per pass (dbeta, dalpha, palette)
@@ -57,10 +64,8 @@ struct BwTable {                         // rows are private to the warp that ow
   float keep[kTile];                     // 1 / 0 active (in / out of box), -2 valid but idle, -1 no sample
   int sid[kTile];
 };
-struct BwMeta {
-  float keep[kTile];
-  int sid[kTile];
-  int flag[kBwPS];
+struct BwMeta {                          // its own, deeper ring: the gather warps read the flags of tile
+  int flag[kBwPS];                       // it - kBwLag while faster warps already publish tile it + 4
 };
 struct BwIn {                            // per warp: phase-1 inputs of its 16 rows, fetched with cp.async
   float o[16][4];                        // origin (or the explicit point), [3] = depth
@@ -73,6 +78,7 @@ struct BwSmem {
   float a[2][2][nfi_mlp::kStageFloats];
   BwTable tab[kBwNT];
   float df[kBwPS][kBwRows * kBwDfLd];
+  float dfe[kBwE][kBwER * kBwDfLd];
   BwMeta meta[kBwNM];
   float pal[kBwE][48];
   BwIn in[kBwPS];
@@ -174,8 +180,6 @@ __device__ __forceinline__ bool bw_phase1(const Args& a, BwTable& tb, BwMeta& mt
   }
   tb.keep[row] = keep;
   tb.sid[row] = sid;
-  mt.keep[row] = keep;
-  mt.sid[row] = sid;
   return act;
 }
 
@@ -227,21 +231,14 @@ __device__ __forceinline__ void bw_gather(const Args& a, const BwTable& tb, floa
   }
 }
 
-// scatter of the warp's 16 rows of dF (scratch `df`, row-major, kBwDfLd floats per row); `any` = the
-// tile went through the MLP (else only the zero point gradients are written)
-template <bool WANT_PTS>
-__device__ __forceinline__ void bw_scatter(const Args& a, const BwTable& tb, const float* df, int b, int w,
-                                           int lane, int per_image, bool any) {
+// d/d point of the warp's rows of dF (scratch `df`, row-major, kBwDfLd floats per row) from the re-read
+// texels, 8 lanes per texel; `any` = the tile went through the MLP (else zeros are written)
+__device__ __forceinline__ void bw_dpoint(const Args& a, const BwTable& tb, const float* df, int b, int w,
+                                          int lane, int per_image, bool any) {
   const int c4 = lane & 7;
   const float third = 1.f / 3.f;
-  const int64_t img = (int64_t)b * 3 * a.Hp * a.Wp * 128 + c4 * 16;
-  const char* pbase = reinterpret_cast<const char*>(a.planes) + img;
-  char* gbase = reinterpret_cast<char*>(a.g_planes) + img;
-#ifndef NFI_BW_SCAT_UNROLL
-#define NFI_BW_SCAT_UNROLL 1
-#endif
-  constexpr int kScatUnroll = NFI_BW_SCAT_UNROLL;
-#pragma unroll (kScatUnroll)
+  const char* pbase = reinterpret_cast<const char*>(a.planes) + (int64_t)b * 3 * a.Hp * a.Wp * 128 + c4 * 16;
+#pragma unroll 1
   for (int it = 0; it < kBwRows / 4; ++it) {
     const int sl = it * 4 + (lane >> 3);
     const int s = bw_row(w, sl);
@@ -250,61 +247,66 @@ __device__ __forceinline__ void bw_scatter(const Args& a, const BwTable& tb, con
     if (any && keep >= 0.f) {
       float4 g = *reinterpret_cast<const float4*>(&df[sl * kBwDfLd + c4 * 4]);
       g.x *= third; g.y *= third; g.z *= third; g.w *= third;
-      uint4 o[3];
       float4 d[3];
       float4 v[3][4];
 #pragma unroll
       for (int p = 0; p < 3; ++p) {
-        o[p] = tb.toff[p][s];
+        const uint4 o = tb.toff[p][s];
         d[p] = tb.tder[p][s];
-        if (WANT_PTS && !kDbgNoPts) {     // all twelve texel re-reads are in flight before the first atomic is issued
-          v[p][0] = bw_ldg(pbase, o[p].x); v[p][1] = bw_ldg(pbase, o[p].y);
-          v[p][2] = bw_ldg(pbase, o[p].z); v[p][3] = bw_ldg(pbase, o[p].w);
-        }
+        v[p][0] = bw_ldg(pbase, o.x); v[p][1] = bw_ldg(pbase, o.y);
+        v[p][2] = bw_ldg(pbase, o.z); v[p][3] = bw_ldg(pbase, o.w);
       }
-#ifndef NFI_DBG_NORED
-      if (a.g_planes)
-#else
-      if (a.g_planes && g.x == 123.456f)
-#endif
-      {
 #pragma unroll
-        for (int p = 0; p < 3; ++p) {
-          // a clamped neighbour (x1 == x0 at the border) carries weight 0: adding 0 is harmless
-          const float4 wt = bw_weights(d[p]);
-          red_add_v4(reinterpret_cast<float*>(gbase + o[p].x), g.x * wt.x, g.y * wt.x, g.z * wt.x, g.w * wt.x);
-          red_add_v4(reinterpret_cast<float*>(gbase + o[p].y), g.x * wt.y, g.y * wt.y, g.z * wt.y, g.w * wt.y);
-          red_add_v4(reinterpret_cast<float*>(gbase + o[p].z), g.x * wt.z, g.y * wt.z, g.z * wt.z, g.w * wt.z);
-          red_add_v4(reinterpret_cast<float*>(gbase + o[p].w), g.x * wt.w, g.y * wt.w, g.z * wt.w, g.w * wt.w);
-        }
-      }
-      if (WANT_PTS && !kDbgNoPts) {
-#pragma unroll
-        for (int p = 0; p < 3; ++p) {
-          // d/d ix = sum_c g_c ((v01 - v00)(1 - ty) + (v11 - v10) ty), d/d iy likewise
-          // (texel differences first: the four dot products of the raw texels cancel to ~1e-4 relative
-          // in the pose gradient on smooth planes)
-          const float ax = bw_dot4(bw_sub4(v[p][1], v[p][0]), g), bx = bw_dot4(bw_sub4(v[p][3], v[p][2]), g);
-          const float ay = bw_dot4(bw_sub4(v[p][2], v[p][0]), g), by = bw_dot4(bw_sub4(v[p][3], v[p][1]), g);
-          const float gx = fmaf(bx - ax, d[p].y, ax), gy = fmaf(by - ay, d[p].x, ay);
-          gp[nfi_plane_axis_a(p)] = fmaf(gx, d[p].z, gp[nfi_plane_axis_a(p)]);
-          gp[nfi_plane_axis_b(p)] = fmaf(gy, d[p].w, gp[nfi_plane_axis_b(p)]);
-        }
+      for (int p = 0; p < 3; ++p) {
+        // d/d ix = sum_c g_c ((v01 - v00)(1 - ty) + (v11 - v10) ty), d/d iy likewise (texel differences
+        // first: dot products of the raw texels cancel to ~1e-4 relative in the pose gradient)
+        const float ax = bw_dot4(bw_sub4(v[p][1], v[p][0]), g), bx = bw_dot4(bw_sub4(v[p][3], v[p][2]), g);
+        const float ay = bw_dot4(bw_sub4(v[p][2], v[p][0]), g), by = bw_dot4(bw_sub4(v[p][3], v[p][1]), g);
+        const float gx = fmaf(bx - ax, d[p].y, ax), gy = fmaf(by - ay, d[p].x, ay);
+        gp[nfi_plane_axis_a(p)] = fmaf(gx, d[p].z, gp[nfi_plane_axis_a(p)]);
+        gp[nfi_plane_axis_b(p)] = fmaf(gy, d[p].w, gp[nfi_plane_axis_b(p)]);
       }
     }
-    if (WANT_PTS) {
 #pragma unroll
-      for (int c = 0; c < 3; ++c) {
-        gp[c] += __shfl_xor_sync(0xffffffffu, gp[c], 1);
-        gp[c] += __shfl_xor_sync(0xffffffffu, gp[c], 2);
-        gp[c] += __shfl_xor_sync(0xffffffffu, gp[c], 4);
-      }
-      if (c4 == 0 && keep != -1.f) {
-        const int64_t id = (int64_t)b * per_image + tb.sid[s];
-        const float inv_r = 1.f / a.f.scene_range;
-        a.g_points[id * 3 + 0] = gp[0] * inv_r;
-        a.g_points[id * 3 + 1] = gp[1] * inv_r;
-        a.g_points[id * 3 + 2] = gp[2] * inv_r;
+    for (int c = 0; c < 3; ++c) {
+      gp[c] += __shfl_xor_sync(0xffffffffu, gp[c], 1);
+      gp[c] += __shfl_xor_sync(0xffffffffu, gp[c], 2);
+      gp[c] += __shfl_xor_sync(0xffffffffu, gp[c], 4);
+    }
+    if (c4 == 0 && keep != -1.f) {
+      const int64_t id = (int64_t)b * per_image + tb.sid[s];
+      const float inv_r = 1.f / a.f.scene_range;
+      a.g_points[id * 3 + 0] = gp[0] * inv_r;
+      a.g_points[id * 3 + 1] = gp[1] * inv_r;
+      a.g_points[id * 3 + 2] = gp[2] * inv_r;
+    }
+  }
+}
+
+// plane-gradient atomics of NR staged rows of dF (scratch `df`, kBwDfLd floats per row; table rows
+// row0 ..): 8 lanes per sample, each red.global.add.v4.f32 of a warp covers four whole 128-byte texels
+template <int NR>
+__device__ __forceinline__ void bw_scatter_rows(const Args& a, const BwTable& tb, const float* df, int b,
+                                                int row0, int lane) {
+  const int c4 = lane & 7;
+  const float third = 1.f / 3.f;
+  char* gbase = reinterpret_cast<char*>(a.g_planes) + (int64_t)b * 3 * a.Hp * a.Wp * 128 + c4 * 16;
+#pragma unroll 1
+  for (int it = 0; it < NR / 4; ++it) {
+    const int sl = it * 4 + (lane >> 3);
+    const int s = row0 + sl;
+    if (tb.keep[s] >= 0.f) {
+      float4 g = *reinterpret_cast<const float4*>(&df[sl * kBwDfLd + c4 * 4]);
+      g.x *= third; g.y *= third; g.z *= third; g.w *= third;
+#pragma unroll
+      for (int p = 0; p < 3; ++p) {
+        // a clamped neighbour (x1 == x0 at the border) carries weight 0: adding 0 is harmless
+        const uint4 o = tb.toff[p][s];
+        const float4 wt = bw_weights(tb.tder[p][s]);
+        red_add_v4(reinterpret_cast<float*>(gbase + o.x), g.x * wt.x, g.y * wt.x, g.z * wt.x, g.w * wt.x);
+        red_add_v4(reinterpret_cast<float*>(gbase + o.y), g.x * wt.y, g.y * wt.y, g.z * wt.y, g.w * wt.y);
+        red_add_v4(reinterpret_cast<float*>(gbase + o.z), g.x * wt.z, g.y * wt.z, g.z * wt.z, g.w * wt.z);
+        red_add_v4(reinterpret_cast<float*>(gbase + o.w), g.x * wt.w, g.y * wt.w, g.z * wt.w, g.w * wt.w);
       }
     }
   }
@@ -351,7 +353,7 @@ field_bwd_ws_kernel(const Args a) {
     for (int c = 0; c < 2; ++c) {
       nfi_tc::mbar_init(&sm.a_full[c], kBwPS); nfi_tc::mbar_init(&sm.a_empty[c], 1);
       nfi_tc::mbar_init(&sm.acc_full[c], 1);   nfi_tc::mbar_init(&sm.acc_ready[c], kBwE / 2);
-      nfi_tc::mbar_init(&sm.df_full[c], 1);    nfi_tc::mbar_init(&sm.acc_free[c], kBwPS);
+      nfi_tc::mbar_init(&sm.df_full[c], 1);    nfi_tc::mbar_init(&sm.acc_free[c], (WANT_PTS ? kBwPS : 0) + kBwE / 2);
     }
     for (int i = 0; i < kBwNM; ++i) { nfi_tc::mbar_init(&sm.meta_full[i], kBwPS); nfi_tc::mbar_init(&sm.meta_empty[i], kBwE / 2 + 1); }
     nfi_tc::mbar_fence_init();
@@ -381,7 +383,10 @@ field_bwd_ws_kernel(const Args a) {
         const int b = (int)(it / (uint32_t)ntile), t = tm.tile((int)(it % (uint32_t)ntile));
         BwTable& tb = sm.tab[it % kBwNT];
         BwMeta& mt = sm.meta[m];
-        nfi_tc::mbar_wait(&sm.meta_empty[m], ((it / kBwNM) & 1) ^ 1);
+        if (it >= (uint32_t)kBwNT) {                       // table slot: tile it - kBwNT scattered (implies meta slot free)
+          const uint32_t r = it - kBwNT;
+          nfi_tc::mbar_wait(&sm.meta_empty[r % kBwNM], (r / kBwNM) & 1);
+        }
         if (w == 0 && lane == 0) NFI_BTRACE(0, it, 0);
         bool act = false;
         cp_async_wait_all();
@@ -403,7 +408,9 @@ field_bwd_ws_kernel(const Args a) {
         if (lane == 0) nfi_tc::mbar_arrive(&sm.a_full[c]);
         if (w == 0 && lane == 0) NFI_BTRACE(0, it, 3);
       }
-      if (it >= (uint32_t)kBwLag) {
+      if (WANT_PTS && it >= (uint32_t)kBwLag) {
+        // d/d point of tile it - kBwLag from its dF rows (read straight out of TMEM) and the re-read
+        // texels; the plane-gradient atomics of the tile are issued by its epilogue group
         const uint32_t j = it - kBwLag, jm = j % kBwNM, c = j & 1;
         const int b = (int)(j / (uint32_t)ntile);
         const BwTable& tb = sm.tab[j % kBwNT];
@@ -419,7 +426,7 @@ field_bwd_ws_kernel(const Args a) {
           nfi_tc::tmem_ld16(tl, v0);
           nfi_tc::tmem_ld16(tl + 16, v1);
           nfi_tc::tmem_ld_wait();
-          __syncwarp();                                   // the previous tile's scatter has read the scratch
+          __syncwarp();                                   // the previous tile's pass has read the scratch
           if (lane / kBwRows == (w >> 2)) {
             float* dst = &sm.df[w][(lane % kBwRows) * kBwDfLd];
 #pragma unroll
@@ -433,9 +440,7 @@ field_bwd_ws_kernel(const Args a) {
           if (lane == 0) nfi_tc::mbar_arrive(&sm.acc_free[c]);
           if (w == 0 && lane == 0) NFI_BTRACE(1, j, 2);
         }
-#ifndef NFI_DBG_NOSCAT
-        if (any || WANT_PTS) bw_scatter<WANT_PTS>(a, tb, sm.df[w], b, w, lane, per_image, any);
-#endif
+        bw_dpoint(a, tb, sm.df[w], b, w, lane, per_image, any);
         if (w == 0 && lane == 0) NFI_BTRACE(1, j, 3);
       }
     }
@@ -452,7 +457,7 @@ field_bwd_ws_kernel(const Args a) {
     float* pal = sm.pal[ew];
     float acc0 = 0.f, acc1 = 0.f;                  // per-lane sums of reduction slots lane, 32 + lane
     int cur_b = -1;
-    uint32_t ph = 0;
+    uint32_t ph = 0, dfph = 0;
     auto flush = [&]() {
       if (cur_b < 0) return;
       const int pbase = NFI_HID * NFI_C + NFI_HID + a.f.n_out * NFI_HID + a.f.n_out;
@@ -466,8 +471,9 @@ field_bwd_ws_kernel(const Args a) {
       const BwMeta& mt = sm.meta[m];
       const int b = (int)(it / (uint32_t)ntile);
       nfi_tc::mbar_wait(&sm.meta_full[m], (it / kBwNM) & 1);
-      const int sid = mt.sid[row];
-      const float keep = mt.keep[row];
+      const BwTable& tb = sm.tab[it % kBwNT];
+      const int sid = tb.sid[row];
+      const float keep = tb.keep[row];
       const bool any = bw_any(mt) != 0;
       if (any) {
         if (b != cur_b) {
@@ -558,6 +564,35 @@ field_bwd_ws_kernel(const Args a) {
         __syncwarp();
         if (lane == 0) nfi_tc::mbar_arrive(&sm.acc_ready[c]);
         if ((ew & 3) == 0 && lane == 0) NFI_BTRACE(3, it, 1);
+        // ---- dF -> plane gradients: this thread's row of dF, 8 x 16-byte atomics per texel
+        nfi_tc::mbar_wait(&sm.df_full[c], dfph); dfph ^= 1;
+        nfi_tc::fence_after_sync();
+        float g0[16], g1[16];
+        nfi_tc::tmem_ld16(tl + nfi_mlp::kColDF, g0);
+        nfi_tc::tmem_ld16(tl + nfi_mlp::kColDF + 16, g1);
+        nfi_tc::tmem_ld_wait();
+        nfi_tc::fence_before_sync();
+        __syncwarp();
+        if (lane == 0) nfi_tc::mbar_arrive(&sm.acc_free[c]);      // the set may take its next tile
+        if ((ew & 3) == 0 && lane == 0) NFI_BTRACE(3, it, 2);
+        if (a.g_planes) {
+          float* sc = sm.dfe[ew];
+#pragma unroll 1
+          for (int h = 0; h < 32 / kBwER; ++h) {          // kBwER rows through the warp's scratch at a time
+            __syncwarp();
+            if (lane / kBwER == h) {
+              float* dst = sc + (lane % kBwER) * kBwDfLd;
+#pragma unroll
+              for (int q = 0; q < 4; ++q) {
+                *reinterpret_cast<float4*>(dst + 4 * q) = make_float4(g0[4 * q], g0[4 * q + 1], g0[4 * q + 2], g0[4 * q + 3]);
+                *reinterpret_cast<float4*>(dst + 16 + 4 * q) = make_float4(g1[4 * q], g1[4 * q + 1], g1[4 * q + 2], g1[4 * q + 3]);
+              }
+            }
+            __syncwarp();
+            bw_scatter_rows<kBwER>(a, tb, sc, b, (ew & 3) * 32 + h * kBwER, lane);
+          }
+        }
+        if ((ew & 3) == 0 && lane == 0) NFI_BTRACE(3, it, 3);
       }
       __syncwarp();
       if (lane == 0) nfi_tc::mbar_arrive(&sm.meta_empty[m]);
