@@ -1,71 +1,72 @@
 // Warp-specialised, software-pipelined backward of the fused triplane field (one persistent CTA per
 // SM, 17 warps).  Same tiling as the forward (nfi_field_fwd_ws.cuh): tile = 128 samples = an 8 x 16
-// pixel block at one depth index = the 128 TMEM lanes; tile `it` lives in accumulator set it & 1.
+// pixel block at one depth index = the 128 TMEM lanes.
 //
-//   gather / scatter (8 warps)  warp w owns 16 rows of every tile end to end: phase 1 (coords, upstream
-//        gradient -> activity, texel offsets, bilinear fractions) -> gather of tile it into operand
-//        stage it & 1 -> then, for tile it - 2, reads its rows of dF straight out of TMEM, scatters
-//        them into the gradient planes (red.global.add.v4.f32) and forms d/d point from the re-read
-//        texels.  The tables of a tile never leave the warp that wrote them.
-//   MMA issuer (1 thread)       per-set state machine, polled: layer 0 (needs the operand stage and the
-//        set to be free) -> layer 1 -> dH = dY . W1 -> dF = dHpre . W0; tcgen05.commit -> mbarriers.
-//   epilogue (2 groups x 4)     group c serves set c, one sample row per thread: softplus (H stays in
-//        TMEM) -> heads forward + backward -> dY -> dHpre = dH * sigmoid.  While a group waits for
-//        its MMAs the other group computes.
+// Every texel line is fetched from L2 exactly once per sample: the gather that recomputes the features
+// F also forms, from the same registers, the tangents T_k = dF / dx_k (k = 0..2, 32 channels each) and
+// parks them in TMEM until the feature gradient dF of the tile comes out of the MLP chain; the point
+// gradient is then three 32-term dot products per sample, taken row-per-thread straight from TMEM.
 //
-// Barriers (c = set, m = meta slot):
-//   meta_full[m]  gather -> MMA, epilogue, scatter   keep / id / activity flags of a tile written
-//   meta_empty[m] epilogue group + MMA -> gather
-//   a_full[c]     gather -> MMA                      operand stage c written
-//   a_empty[c]    MMA (commit) -> gather             layer 0 of the tile in stage c has read it
-//   acc_full[c]   MMA (commit) -> epilogue group c   next accumulator of the chain is complete
-//   acc_ready[c]  epilogue group c -> MMA            next A operand (H, dY, dHpre) is in TMEM
-//   df_full[c]    MMA (commit) -> scatter            dF of the tile in set c is complete
-//   acc_free[c]   scatter -> MMA                     dF has been read: set c may take a new tile
+//   gather (8 warps)     warp w owns 16 rows of every tile: phase 1 (coords, upstream gradient ->
+//        activity, texel offsets, bilinear fractions) -> gather -> F into operand stage it & 1 (shared
+//        memory, hi / lo), T through a per-quarter transposition scratch into TMEM buffer it & 1.
+//   MMA issuer (1 warp, one elected lane)  layer 0 -> layer 1 -> dH = dY . W1 -> dF = dHpre . W0, each
+//        after the epilogue stage before it; tcgen05.commit -> mbarriers.  One accumulator set.
+//   epilogue (4 warps)   one sample row per thread: softplus (H stays in TMEM) -> heads forward +
+//        backward -> dY -> dHpre = dH * sigmoid; per-image palette / beta / alpha sums.
+//   scatter (4 warps)    one sample row per thread: dF and T from TMEM -> d/d point; then the rows of
+//        dF go through shared memory 8 at a time so that 8 lanes cover one texel line of the gradient
+//        planes with red.global.add.v4.f32.  Runs one tile behind the epilogue warps.
+//
+// TMEM (512 columns): [0,240) the chain (nfi_mlp_tc.cuh) | [240,432) T, two buffers of 96 |
+//                     [432,496) dF, two buffers of 32
+//
+// Barriers (c = it & 1, m = flag slot):
+//   meta_full[m]  gather -> everyone                 tables + activity flags of a tile written
+//   meta_empty[m] epilogue + scatter + MMA -> gather tile finished: its table slot may be rewritten
+//   a_full[c]     gather -> MMA                      F stage c and T buffer c written (or tile idle)
+//   a_empty[c]    MMA (commit) -> gather             layer 0 has read stage c
+//   acc_full      MMA (commit) -> epilogue           next accumulator of the chain is complete
+//   acc_ready     epilogue -> MMA                    next A operand (H, dY, dHpre) is in TMEM
+//   df_full[c]    MMA (commit) -> scatter            dF buffer c is complete
+//   s_free[c]     scatter -> gather                  T and dF buffers c have been read (every tile)
 #pragma once
 #include "nfi_field_tc.cuh"
 
 namespace nfi_ftc {
 
-#ifndef NFI_BW_PS
-#define NFI_BW_PS 8
-#endif
-constexpr int kBwPS = NFI_BW_PS;         // gather / scatter warps (8 or 16)
+constexpr int kBwPS = 8;                 // gather warps
 constexpr int kBwRows = kTile / kBwPS;   // rows of a tile owned by one of them
-constexpr int kBwE = 8;                  // epilogue warps (2 groups of 4)
-constexpr int kBwThreads = (kBwPS + kBwE + 1) * 32;     // 544
+constexpr int kBwE = 4;                  // epilogue warps (warp_id % 4 = TMEM lane quarter)
+constexpr int kBwS = 4;                  // scatter warps (likewise)
+constexpr int kBwThreads = (kBwPS + kBwE + kBwS + 1) * 32;     // 544
 #ifndef NFI_BW_EROWS
 #define NFI_BW_EROWS 8
 #endif
 #ifndef NFI_BW_RING
 #define NFI_BW_RING 3
 #endif
-constexpr int kBwNT = NFI_BW_RING;       // table ring: a slot is free once the tile's epilogue group has scattered it
-constexpr int kBwER = NFI_BW_EROWS;      // rows of dF an epilogue warp stages at a time for its atomics
-constexpr int kBwNM = 8;               // ring of tables + meta: a slot is free once the epilogue group has scattered its tile
-constexpr int kBwLag = 2;                // scatter runs this many tiles behind the gather
+constexpr int kBwNT = NFI_BW_RING;       // table ring: a slot is free once the tile has been scattered
+constexpr int kBwER = NFI_BW_EROWS;      // rows of dF a scatter warp stages at a time for its atomics
+constexpr int kBwNM = 8;                 // ring of activity flags (deeper: read by warps that lag)
 constexpr int kBwDfLd = 36;              // dF scratch row stride (floats)
+constexpr int kBwTLd = 100;              // T scratch row stride (floats): 96 + 4, conflict-free both ways
 constexpr int kBwRed = 32;               // per-image scalar gradients reduced per pass (dbeta, dalpha, palette)
+constexpr int kBwColT = 240, kBwColDF = 432, kBwTmemCols = 512;
 
 __device__ __forceinline__ void red_add_v4(float* addr, float a, float b, float c, float d) {
   asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(addr), "f"(a), "f"(b), "f"(c), "f"(d)
                : "memory");
 }
 
-#ifdef NFI_DBG_NOPTS
-constexpr bool kDbgNoPts = true;
-#else
-constexpr bool kDbgNoPts = false;
-#endif
-
-struct BwTable {                         // rows are private to the warp that owns them
+struct BwTable {                         // rows are written by the gather warp that owns them
   uint4 toff[3][kTile];                  // byte offsets of the 4 texels from the image's first plane
   float4 tder[3][kTile];                 // tx, ty, d ix / d x_a, d iy / d x_b (0 where clamped)
   float keep[kTile];                     // 1 / 0 active (in / out of box), -2 valid but idle, -1 no sample
   int sid[kTile];
 };
-struct BwMeta {                          // its own, deeper ring: the gather warps read the flags of tile
-  int flag[kBwPS];                       // it - kBwLag while faster warps already publish tile it + 4
+struct BwMeta {
+  int flag[kBwPS];
 };
 struct BwIn {                            // per warp: phase-1 inputs of its 16 rows, fetched with cp.async
   float o[16][4];                        // origin (or the explicit point), [3] = depth
@@ -77,12 +78,12 @@ struct BwSmem {
   nfi_mlp::BwdWeights bw;
   float a[2][2][nfi_mlp::kStageFloats];
   BwTable tab[kBwNT];
-  float df[kBwPS][kBwRows * kBwDfLd];
-  float dfe[kBwE][kBwER * kBwDfLd];
+  float tq[4][32 * kBwTLd];              // per lane quarter: T rows of the tile being gathered
+  float dfe[kBwS][kBwER * kBwDfLd];
   BwMeta meta[kBwNM];
   float pal[kBwE][48];
   BwIn in[kBwPS];
-  uint64_t a_full[2], a_empty[2], acc_full[2], acc_ready[2], df_full[2], acc_free[2];
+  uint64_t a_full[2], a_empty[2], df_full[2], s_free[2], acc_full, acc_ready;
   uint64_t meta_full[kBwNM], meta_empty[kBwNM];
   uint32_t tmem_base;
   uint32_t pad;
@@ -95,8 +96,8 @@ __device__ __forceinline__ int bw_any(const BwMeta& m) {
   return f;
 }
 
-// rows of gather/scatter warp w: the 16 TMEM lanes [16 (w >> 2), +16) of lane quarter w & 3, so the
-// warp can read its rows of dF with tcgen05.ld (a warp only reaches the quarter warp_id % 4)
+// rows of gather warp w: the 16 TMEM lanes [16 (w >> 2), +16) of lane quarter w & 3 (warps w and
+// w + 4 share a quarter: together they can write its 32 lanes with tcgen05.st)
 __device__ __forceinline__ int bw_row(int w, int i) { return 32 * (w & 3) + kBwRows * (w >> 2) + i; }
 
 __device__ __forceinline__ void cp_async4(void* dst, const void* src) {
@@ -128,7 +129,7 @@ __device__ __forceinline__ void bw_prefetch(const Args& a, BwIn& in, int b, int 
 
 // phase 1 of one sample: activity from the upstream gradient, texel offsets, fractions
 template <bool PTS, int MODE>
-__device__ __forceinline__ bool bw_phase1(const Args& a, BwTable& tb, BwMeta& mt, const BwIn& in, int b, int t,
+__device__ __forceinline__ bool bw_phase1(const Args& a, BwTable& tb, const BwIn& in, int b, int t,
                                           int row, int li, int per_image) {
   int ray;
   const int sid = sample_and_ray(a, t, row, ray);
@@ -192,8 +193,9 @@ __device__ __forceinline__ void bw_fma4(float4& acc, const float4& v, float w) {
 __device__ __forceinline__ float4 bw_sub4(const float4& a, const float4& b) {
   return make_float4(a.x - b.x, a.y - b.y, a.z - b.z, a.w - b.w);
 }
-__device__ __forceinline__ float bw_dot4(const float4& v, const float4& g) {
-  return fmaf(v.w, g.w, fmaf(v.z, g.z, fmaf(v.y, g.y, v.x * g.x)));
+// a + (b - a) t
+__device__ __forceinline__ float4 bw_lerp4(const float4& a, const float4& b, float t) {
+  return make_float4(fmaf(b.x - a.x, t, a.x), fmaf(b.y - a.y, t, a.y), fmaf(b.z - a.z, t, a.z), fmaf(b.w - a.w, t, a.w));
 }
 // ATen's bilinear weights from the fractions: (fx + 1) - ix and 1 - tx are the same correctly rounded
 // number (tx = ix - fx is exact), so these are the forward's weights bit for bit
@@ -202,85 +204,74 @@ __device__ __forceinline__ float4 bw_weights(const float4& d) {
   return make_float4(ex * ey, d.x * ey, ex * d.y, d.x * d.y);
 }
 
-// gather of the warp's 16 rows into the operand stage
-__device__ __forceinline__ void bw_gather(const Args& a, const BwTable& tb, float* a_hi, float* a_lo, int b,
-                                          int w, int lane) {
+// gather of the warp's 16 rows: features into the operand stage and, from the same texels, the
+// tangents T_k = dF / dx_k (in units of the normalised coordinate) into the quarter's scratch `tq`
+// (row = TMEM lane within the quarter, kBwTLd floats per row, T_k at [32 k, 32 k + 32)).
+// Texel order: 0 (x0,y0)  1 (x1,y0)  2 (x0,y1)  3 (x1,y1).
+//   dF/d ix = (v1 - v0) + ((v3 - v2) - (v1 - v0)) ty      dF/d iy = (v2 - v0) + ((v3 - v1) - (v2 - v0)) tx
+// (texel differences first: sums of the raw texels cancel to ~1e-4 relative in the pose gradient)
+template <bool WANT_PTS>
+__device__ __forceinline__ void bw_gather(const Args& a, const BwTable& tb, float* a_hi, float* a_lo, float* tq,
+                                          int b, int w, int lane) {
   const int c4 = lane & 7;
   const float third = 1.f / 3.f;
   const char* base = reinterpret_cast<const char*>(a.planes) + (int64_t)b * 3 * a.Hp * a.Wp * 128 + c4 * 16;
-#pragma unroll 2
+#pragma unroll 1
   for (int it = 0; it < kBwRows / 4; ++it) {
-    const int s = bw_row(w, it * 4 + (lane >> 3));
+    const int li = it * 4 + (lane >> 3);
+    const int s = bw_row(w, li);
     float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
     if (tb.keep[s] >= 0.f) {
       float4 v[3][4];
-      float4 wt[3];
+      float4 d[3];
 #pragma unroll
       for (int p = 0; p < 3; ++p) {
         const uint4 o = tb.toff[p][s];
-        wt[p] = bw_weights(tb.tder[p][s]);
+        d[p] = tb.tder[p][s];
         v[p][0] = bw_ldg(base, o.x); v[p][1] = bw_ldg(base, o.y); v[p][2] = bw_ldg(base, o.z); v[p][3] = bw_ldg(base, o.w);
       }
+      float4 t[3];
+#pragma unroll
+      for (int k = 0; k < 3; ++k) t[k] = make_float4(0.f, 0.f, 0.f, 0.f);
 #pragma unroll
       for (int p = 0; p < 3; ++p) {
-        bw_fma4(acc, v[p][0], wt[p].x * third); bw_fma4(acc, v[p][1], wt[p].y * third);
-        bw_fma4(acc, v[p][2], wt[p].z * third); bw_fma4(acc, v[p][3], wt[p].w * third);
+        const float4 wt = bw_weights(d[p]);
+        bw_fma4(acc, v[p][0], wt.x * third); bw_fma4(acc, v[p][1], wt.y * third);
+        bw_fma4(acc, v[p][2], wt.z * third); bw_fma4(acc, v[p][3], wt.w * third);
+        if (WANT_PTS) {
+          const float4 gx = bw_lerp4(bw_sub4(v[p][1], v[p][0]), bw_sub4(v[p][3], v[p][2]), d[p].y);
+          const float4 gy = bw_lerp4(bw_sub4(v[p][2], v[p][0]), bw_sub4(v[p][3], v[p][1]), d[p].x);
+          bw_fma4(t[nfi_plane_axis_a(p)], gx, d[p].z * third);
+          bw_fma4(t[nfi_plane_axis_b(p)], gy, d[p].w * third);
+        }
+      }
+      if (WANT_PTS) {
+        float* dst = tq + (kBwRows * (w >> 2) + li) * kBwTLd + c4 * 4;
+#pragma unroll
+        for (int k = 0; k < 3; ++k) *reinterpret_cast<float4*>(dst + 32 * k) = t[k];
       }
     }
     nfi_mlp::store_feat4(a_hi, a_lo, s, c4, acc);
   }
 }
 
-// d/d point of the warp's rows of dF (scratch `df`, row-major, kBwDfLd floats per row) from the re-read
-// texels, 8 lanes per texel; `any` = the tile went through the MLP (else zeros are written)
-__device__ __forceinline__ void bw_dpoint(const Args& a, const BwTable& tb, const float* df, int b, int w,
-                                          int lane, int per_image, bool any) {
-  const int c4 = lane & 7;
-  const float third = 1.f / 3.f;
-  const char* pbase = reinterpret_cast<const char*>(a.planes) + (int64_t)b * 3 * a.Hp * a.Wp * 128 + c4 * 16;
-#pragma unroll 1
-  for (int it = 0; it < kBwRows / 4; ++it) {
-    const int sl = it * 4 + (lane >> 3);
-    const int s = bw_row(w, sl);
-    const float keep = tb.keep[s];
-    float gp[3] = {0.f, 0.f, 0.f};
-    if (any && keep >= 0.f) {
-      float4 g = *reinterpret_cast<const float4*>(&df[sl * kBwDfLd + c4 * 4]);
-      g.x *= third; g.y *= third; g.z *= third; g.w *= third;
-      float4 d[3];
-      float4 v[3][4];
+// T rows of a lane quarter: scratch -> TMEM.  The two warps of the quarter take 48 columns each of all
+// 32 lanes (thread i <-> lane i of the quarter); rows that were not gathered carry stale values that
+// no one uses.
+__device__ __forceinline__ void bw_store_t(const float* tq, uint32_t tmem_t, int half, int lane) {
+  const float* src = tq + lane * kBwTLd + 48 * half;
 #pragma unroll
-      for (int p = 0; p < 3; ++p) {
-        const uint4 o = tb.toff[p][s];
-        d[p] = tb.tder[p][s];
-        v[p][0] = bw_ldg(pbase, o.x); v[p][1] = bw_ldg(pbase, o.y);
-        v[p][2] = bw_ldg(pbase, o.z); v[p][3] = bw_ldg(pbase, o.w);
-      }
+  for (int j = 0; j < 3; ++j) {
+    uint32_t r[16];
 #pragma unroll
-      for (int p = 0; p < 3; ++p) {
-        // d/d ix = sum_c g_c ((v01 - v00)(1 - ty) + (v11 - v10) ty), d/d iy likewise (texel differences
-        // first: dot products of the raw texels cancel to ~1e-4 relative in the pose gradient)
-        const float ax = bw_dot4(bw_sub4(v[p][1], v[p][0]), g), bx = bw_dot4(bw_sub4(v[p][3], v[p][2]), g);
-        const float ay = bw_dot4(bw_sub4(v[p][2], v[p][0]), g), by = bw_dot4(bw_sub4(v[p][3], v[p][1]), g);
-        const float gx = fmaf(bx - ax, d[p].y, ax), gy = fmaf(by - ay, d[p].x, ay);
-        gp[nfi_plane_axis_a(p)] = fmaf(gx, d[p].z, gp[nfi_plane_axis_a(p)]);
-        gp[nfi_plane_axis_b(p)] = fmaf(gy, d[p].w, gp[nfi_plane_axis_b(p)]);
-      }
+    for (int q = 0; q < 4; ++q) {
+      const float4 v = *reinterpret_cast<const float4*>(src + 16 * j + 4 * q);
+      r[4 * q] = __float_as_uint(v.x); r[4 * q + 1] = __float_as_uint(v.y);
+      r[4 * q + 2] = __float_as_uint(v.z); r[4 * q + 3] = __float_as_uint(v.w);
     }
-#pragma unroll
-    for (int c = 0; c < 3; ++c) {
-      gp[c] += __shfl_xor_sync(0xffffffffu, gp[c], 1);
-      gp[c] += __shfl_xor_sync(0xffffffffu, gp[c], 2);
-      gp[c] += __shfl_xor_sync(0xffffffffu, gp[c], 4);
-    }
-    if (c4 == 0 && keep != -1.f) {
-      const int64_t id = (int64_t)b * per_image + tb.sid[s];
-      const float inv_r = 1.f / a.f.scene_range;
-      a.g_points[id * 3 + 0] = gp[0] * inv_r;
-      a.g_points[id * 3 + 1] = gp[1] * inv_r;
-      a.g_points[id * 3 + 2] = gp[2] * inv_r;
-    }
+    nfi_tc::tmem_st16(tmem_t + 48 * half + 16 * j, r);
   }
+  nfi_tc::tmem_st_wait();
 }
 
 // plane-gradient atomics of NR staged rows of dF (scratch `df`, kBwDfLd floats per row; table rows
@@ -351,14 +342,19 @@ field_bwd_ws_kernel(const Args a) {
   nfi_mlp::load_weights_bwd(sm.bw, a.f.W0, a.f.W1, a.f.n_out);
   if (tid == 0) {
     for (int c = 0; c < 2; ++c) {
-      nfi_tc::mbar_init(&sm.a_full[c], kBwPS); nfi_tc::mbar_init(&sm.a_empty[c], 1);
-      nfi_tc::mbar_init(&sm.acc_full[c], 1);   nfi_tc::mbar_init(&sm.acc_ready[c], kBwE / 2);
-      nfi_tc::mbar_init(&sm.df_full[c], 1);    nfi_tc::mbar_init(&sm.acc_free[c], (WANT_PTS ? kBwPS : 0) + kBwE / 2);
+      nfi_tc::mbar_init(&sm.a_full[c], kBwPS);  nfi_tc::mbar_init(&sm.a_empty[c], 1);
+      nfi_tc::mbar_init(&sm.df_full[c], 1);     nfi_tc::mbar_init(&sm.s_free[c], kBwS);
     }
-    for (int i = 0; i < kBwNM; ++i) { nfi_tc::mbar_init(&sm.meta_full[i], kBwPS); nfi_tc::mbar_init(&sm.meta_empty[i], kBwE / 2 + 1); }
+    nfi_tc::mbar_init(&sm.acc_full, 1);
+    nfi_tc::mbar_init(&sm.acc_ready, kBwE);
+    for (int i = 0; i < kBwNM; ++i) {
+      nfi_tc::mbar_init(&sm.meta_full[i], kBwPS);
+      nfi_tc::mbar_init(&sm.meta_empty[i], kBwE + kBwS + 1);
+    }
     nfi_tc::mbar_fence_init();
   }
-  if (warp == kBwPS + kBwE) nfi_tc::tmem_alloc(&sm.tmem_base, 2 * nfi_mlp::kTmemCols);
+  constexpr int kMmaWarp = kBwPS + kBwE + kBwS;
+  if (warp == kMmaWarp) nfi_tc::tmem_alloc(&sm.tmem_base, kBwTmemCols);
   nfi_tc::fence_proxy_async();
   nfi_tc::fence_before_sync();
   __syncthreads();
@@ -370,85 +366,56 @@ field_bwd_ws_kernel(const Args a) {
   const uint32_t total = (uint32_t)a.B * (uint32_t)ntile;
 
   if (warp < kBwPS) {
-    // ------------------------------------------------------------------ gather / scatter
-    const int w = warp;
+    // ------------------------------------------------------------------ gather
+    const int w = warp, q = w & 3, half = w >> 2;
     const int row = bw_row(w, lane & (kBwRows - 1));
-    const uint32_t lane_off = (uint32_t)((w & 3) * 32) << 16;
-    uint32_t df_ph[2] = {0, 0};
+    const uint32_t lane_off = (uint32_t)(q * 32) << 16;
     BwIn& in = sm.in[w];
     if (lane < kBwRows && total > 0) bw_prefetch<PTS, MODE>(a, in, 0, tm.tile(0), row, lane, per_image);
-    for (uint32_t it = 0; it < total + kBwLag; ++it) {
-      if (it < total) {
-        const uint32_t m = it % kBwNM, c = it & 1;
-        const int b = (int)(it / (uint32_t)ntile), t = tm.tile((int)(it % (uint32_t)ntile));
-        BwTable& tb = sm.tab[it % kBwNT];
-        BwMeta& mt = sm.meta[m];
-        if (it >= (uint32_t)kBwNT) {                       // table slot: tile it - kBwNT scattered (implies meta slot free)
-          const uint32_t r = it - kBwNT;
-          nfi_tc::mbar_wait(&sm.meta_empty[r % kBwNM], (r / kBwNM) & 1);
-        }
-        if (w == 0 && lane == 0) NFI_BTRACE(0, it, 0);
-        bool act = false;
-        cp_async_wait_all();
-        if (lane < kBwRows) act = bw_phase1<PTS, MODE>(a, tb, mt, in, b, t, row, lane, per_image);
-        const unsigned wany = __any_sync(0xffffffffu, act);
-        if (lane == 0) mt.flag[w] = wany ? 1 : 0;
-        __syncwarp();
-        if (lane == 0) nfi_tc::mbar_arrive(&sm.meta_full[m]);
-        if (lane < kBwRows && it + 1 < total) {            // inputs of the next tile arrive during gather + scatter
-          const uint32_t n = it + 1;
-          bw_prefetch<PTS, MODE>(a, in, (int)(n / (uint32_t)ntile), tm.tile((int)(n % (uint32_t)ntile)), row, lane, per_image);
-        }
-        if (w == 0 && lane == 0) NFI_BTRACE(0, it, 1);
-        nfi_tc::mbar_wait(&sm.a_empty[c], ((it >> 1) & 1) ^ 1);
+    for (uint32_t it = 0; it < total; ++it) {
+      const uint32_t m = it % kBwNM, c = it & 1;
+      const int b = (int)(it / (uint32_t)ntile), t = tm.tile((int)(it % (uint32_t)ntile));
+      BwTable& tb = sm.tab[it % kBwNT];
+      if (it >= (uint32_t)kBwNT) {                       // table slot: tile it - kBwNT is finished
+        const uint32_t r = it - kBwNT;
+        nfi_tc::mbar_wait(&sm.meta_empty[r % kBwNM], (r / kBwNM) & 1);
+      }
+      if (w == 0 && lane == 0) NFI_BTRACE(0, it, 0);
+      bool act = false;
+      cp_async_wait_all();
+      if (lane < kBwRows) act = bw_phase1<PTS, MODE>(a, tb, in, b, t, row, lane, per_image);
+      const unsigned wany = __any_sync(0xffffffffu, act);
+      if (lane == 0) sm.meta[m].flag[w] = wany ? 1 : 0;
+      __syncwarp();
+      if (lane == 0) nfi_tc::mbar_arrive(&sm.meta_full[m]);
+      if (lane < kBwRows && it + 1 < total) {            // inputs of the next tile arrive during the gather
+        const uint32_t n = it + 1;
+        bw_prefetch<PTS, MODE>(a, in, (int)(n / (uint32_t)ntile), tm.tile((int)(n % (uint32_t)ntile)), row, lane, per_image);
+      }
+      if (w == 0 && lane == 0) NFI_BTRACE(0, it, 1);
+      nfi_tc::mbar_wait(&sm.meta_full[m], (it / kBwNM) & 1);          // the flags of all eight warps
+      if (bw_any(sm.meta[m])) {
+        nfi_tc::mbar_wait(&sm.a_empty[c], ((it >> 1) & 1) ^ 1);       // layer 0 of tile it - 2 has read stage c
+        if (it >= 2) nfi_tc::mbar_wait(&sm.s_free[c], ((it >> 1) - 1) & 1);   // T / dF buffers c read
         if (w == 0 && lane == 0) NFI_BTRACE(0, it, 2);
-        if (wany) bw_gather(a, tb, sm.a[c][0], sm.a[c][1], b, w, lane);
-        nfi_tc::fence_proxy_async();
-        __syncwarp();
-        if (lane == 0) nfi_tc::mbar_arrive(&sm.a_full[c]);
-        if (w == 0 && lane == 0) NFI_BTRACE(0, it, 3);
-      }
-      if (WANT_PTS && it >= (uint32_t)kBwLag) {
-        // d/d point of tile it - kBwLag from its dF rows (read straight out of TMEM) and the re-read
-        // texels; the plane-gradient atomics of the tile are issued by its epilogue group
-        const uint32_t j = it - kBwLag, jm = j % kBwNM, c = j & 1;
-        const int b = (int)(j / (uint32_t)ntile);
-        const BwTable& tb = sm.tab[j % kBwNT];
-        nfi_tc::mbar_wait(&sm.meta_full[jm], (j / kBwNM) & 1);       // completed long ago: flags of all warps
-        const bool any = bw_any(sm.meta[jm]) != 0;
-        if (w == 0 && lane == 0) NFI_BTRACE(1, j, 0);
-        if (any) {
-          nfi_tc::mbar_wait(&sm.df_full[c], df_ph[c]); df_ph[c] ^= 1;
-          if (w == 0 && lane == 0) NFI_BTRACE(1, j, 1);
-          nfi_tc::fence_after_sync();
-          float v0[16], v1[16];
-          const uint32_t tl = tmem + c * nfi_mlp::kTmemCols + lane_off + nfi_mlp::kColDF;
-          nfi_tc::tmem_ld16(tl, v0);
-          nfi_tc::tmem_ld16(tl + 16, v1);
-          nfi_tc::tmem_ld_wait();
-          __syncwarp();                                   // the previous tile's pass has read the scratch
-          if (lane / kBwRows == (w >> 2)) {
-            float* dst = &sm.df[w][(lane % kBwRows) * kBwDfLd];
-#pragma unroll
-            for (int q = 0; q < 4; ++q) {
-              *reinterpret_cast<float4*>(dst + 4 * q) = make_float4(v0[4 * q], v0[4 * q + 1], v0[4 * q + 2], v0[4 * q + 3]);
-              *reinterpret_cast<float4*>(dst + 16 + 4 * q) = make_float4(v1[4 * q], v1[4 * q + 1], v1[4 * q + 2], v1[4 * q + 3]);
-            }
-          }
+        bw_gather<WANT_PTS>(a, tb, sm.a[c][0], sm.a[c][1], sm.tq[q], b, w, lane);
+        if (WANT_PTS) {
+          nfi_tc::named_bar_sync(1 + q, 64);             // both halves of the quarter are in the scratch
+          bw_store_t(sm.tq[q], tmem + lane_off + kBwColT + 96 * c, half, lane);
+          nfi_tc::named_bar_sync(1 + q, 64);             // ... and have been read: the scratch is free
           nfi_tc::fence_before_sync();
-          __syncwarp();
-          if (lane == 0) nfi_tc::mbar_arrive(&sm.acc_free[c]);
-          if (w == 0 && lane == 0) NFI_BTRACE(1, j, 2);
         }
-        bw_dpoint(a, tb, sm.df[w], b, w, lane, per_image, any);
-        if (w == 0 && lane == 0) NFI_BTRACE(1, j, 3);
+        nfi_tc::fence_proxy_async();
       }
+      __syncwarp();
+      if (lane == 0) nfi_tc::mbar_arrive(&sm.a_full[c]);
+      if (w == 0 && lane == 0) NFI_BTRACE(0, it, 3);
     }
   } else if (warp < kBwPS + kBwE) {
-    // ------------------------------------------------------------------ epilogue group c <-> set c
-    const int ew = warp - kBwPS, c = ew >> 2;
-    const int row = (ew & 3) * 32 + lane;
-    const uint32_t tl = tmem + c * nfi_mlp::kTmemCols + ((uint32_t)((ew & 3) * 32) << 16);
+    // ------------------------------------------------------------------ epilogue: the MLP chain
+    const int ew = warp - kBwPS;
+    const int row = ew * 32 + lane;
+    const uint32_t tl = tmem + ((uint32_t)(ew * 32) << 16);
     const NfiHeads hd = make_heads(a.f);
     const int npal = 3 * hd.A;
     const bool want_pal = MODE == 0 && a.g_palette != nullptr && hd.A > 0;
@@ -457,7 +424,7 @@ field_bwd_ws_kernel(const Args a) {
     float* pal = sm.pal[ew];
     float acc0 = 0.f, acc1 = 0.f;                  // per-lane sums of reduction slots lane, 32 + lane
     int cur_b = -1;
-    uint32_t ph = 0, dfph = 0;
+    uint32_t ph = 0;
     auto flush = [&]() {
       if (cur_b < 0) return;
       const int pbase = NFI_HID * NFI_C + NFI_HID + a.f.n_out * NFI_HID + a.f.n_out;
@@ -466,16 +433,14 @@ field_bwd_ws_kernel(const Args a) {
       if (want_pal && kBwRed - 2 + lane < npal && acc1 != 0.f) atomicAdd(&a.g_palette[(int64_t)cur_b * npal + kBwRed - 2 + lane], acc1);
       acc0 = acc1 = 0.f;
     };
-    for (uint32_t it = c; it < total; it += 2) {
+    for (uint32_t it = 0; it < total; ++it) {
       const uint32_t m = it % kBwNM;
-      const BwMeta& mt = sm.meta[m];
       const int b = (int)(it / (uint32_t)ntile);
       nfi_tc::mbar_wait(&sm.meta_full[m], (it / kBwNM) & 1);
       const BwTable& tb = sm.tab[it % kBwNT];
       const int sid = tb.sid[row];
       const float keep = tb.keep[row];
-      const bool any = bw_any(mt) != 0;
-      if (any) {
+      if (bw_any(sm.meta[m])) {
         if (b != cur_b) {
           flush();
           cur_b = b;
@@ -500,24 +465,24 @@ field_bwd_ws_kernel(const Args a) {
           }
         }
         // ---- layer 0 -> H
-        nfi_tc::mbar_wait(&sm.acc_full[c], ph); ph ^= 1;
-        if ((ew & 3) == 0 && lane == 0) NFI_BTRACE(2, it, 0);
+        nfi_tc::mbar_wait(&sm.acc_full, ph); ph ^= 1;
+        if (ew == 0 && lane == 0) NFI_BTRACE(2, it, 0);
         nfi_tc::fence_after_sync();
         nfi_mlp::epilogue0_at<4>(sm.w.b0, tl, 0);
         nfi_tc::fence_before_sync();
         __syncwarp();
-        if (lane == 0) nfi_tc::mbar_arrive(&sm.acc_ready[c]);
-        if ((ew & 3) == 0 && lane == 0) NFI_BTRACE(2, it, 1);
+        if (lane == 0) nfi_tc::mbar_arrive(&sm.acc_ready);
+        if (ew == 0 && lane == 0) NFI_BTRACE(2, it, 1);
         // ---- layer 1 -> heads forward + backward -> dY
-        nfi_tc::mbar_wait(&sm.acc_full[c], ph); ph ^= 1;
-        if ((ew & 3) == 0 && lane == 0) NFI_BTRACE(2, it, 2);
+        nfi_tc::mbar_wait(&sm.acc_full, ph); ph ^= 1;
+        if (ew == 0 && lane == 0) NFI_BTRACE(2, it, 2);
         nfi_tc::fence_after_sync();
         float dy[NFI_YPAD];
 #pragma unroll
         for (int o = 0; o < NFI_YPAD; ++o) dy[o] = 0.f;
         float probs[NFI_YPAD - 1];                  // zero for idle rows: they add nothing below
 #pragma unroll
-        for (int q = 0; q < NFI_YPAD - 1; ++q) probs[q] = 0.f;
+        for (int i = 0; i < NFI_YPAD - 1; ++i) probs[i] = 0.f;
         const float drgb[3] = {gy[1], gy[2], gy[3]};
         float dbeta = 0.f, dalpha = 0.f;
         if (MODE == 0) {
@@ -537,8 +502,8 @@ field_bwd_ws_kernel(const Args a) {
         nfi_mlp::store_dy(tl, dy);
         nfi_tc::fence_before_sync();
         __syncwarp();
-        if (lane == 0) nfi_tc::mbar_arrive(&sm.acc_ready[c]);
-        if ((ew & 3) == 0 && lane == 0) NFI_BTRACE(2, it, 3);
+        if (lane == 0) nfi_tc::mbar_arrive(&sm.acc_ready);
+        if (ew == 0 && lane == 0) NFI_BTRACE(2, it, 3);
         if (want_pal || want_par) {                 // while the dH MMAs run
           // reduction slots: 0 dbeta, 1 dalpha, 2 + 3 q + k  d palette[q][k] = probs[q] * drgb[k]
           float red[kBwRed];
@@ -556,111 +521,131 @@ field_bwd_ws_kernel(const Args a) {
           }
         }
         // ---- dH -> dHpre
-        nfi_tc::mbar_wait(&sm.acc_full[c], ph); ph ^= 1;
-        if ((ew & 3) == 0 && lane == 0) NFI_BTRACE(3, it, 0);
+        nfi_tc::mbar_wait(&sm.acc_full, ph); ph ^= 1;
+        if (ew == 0 && lane == 0) NFI_BTRACE(3, it, 0);
         nfi_tc::fence_after_sync();
         nfi_mlp::epilogue2<4>(tl, 0);
         nfi_tc::fence_before_sync();
         __syncwarp();
-        if (lane == 0) nfi_tc::mbar_arrive(&sm.acc_ready[c]);
-        if ((ew & 3) == 0 && lane == 0) NFI_BTRACE(3, it, 1);
-        // ---- dF -> plane gradients: this thread's row of dF, 8 x 16-byte atomics per texel
-        nfi_tc::mbar_wait(&sm.df_full[c], dfph); dfph ^= 1;
-        nfi_tc::fence_after_sync();
-        float g0[16], g1[16];
-        nfi_tc::tmem_ld16(tl + nfi_mlp::kColDF, g0);
-        nfi_tc::tmem_ld16(tl + nfi_mlp::kColDF + 16, g1);
-        nfi_tc::tmem_ld_wait();
-        nfi_tc::fence_before_sync();
-        __syncwarp();
-        if (lane == 0) nfi_tc::mbar_arrive(&sm.acc_free[c]);      // the set may take its next tile
-        if ((ew & 3) == 0 && lane == 0) NFI_BTRACE(3, it, 2);
-        if (a.g_planes) {
-          float* sc = sm.dfe[ew];
-#pragma unroll 1
-          for (int h = 0; h < 32 / kBwER; ++h) {          // kBwER rows through the warp's scratch at a time
-            __syncwarp();
-            if (lane / kBwER == h) {
-              float* dst = sc + (lane % kBwER) * kBwDfLd;
-#pragma unroll
-              for (int q = 0; q < 4; ++q) {
-                *reinterpret_cast<float4*>(dst + 4 * q) = make_float4(g0[4 * q], g0[4 * q + 1], g0[4 * q + 2], g0[4 * q + 3]);
-                *reinterpret_cast<float4*>(dst + 16 + 4 * q) = make_float4(g1[4 * q], g1[4 * q + 1], g1[4 * q + 2], g1[4 * q + 3]);
-              }
-            }
-            __syncwarp();
-            bw_scatter_rows<kBwER>(a, tb, sc, b, (ew & 3) * 32 + h * kBwER, lane);
-          }
-        }
-        if ((ew & 3) == 0 && lane == 0) NFI_BTRACE(3, it, 3);
+        if (lane == 0) nfi_tc::mbar_arrive(&sm.acc_ready);
+        if (ew == 0 && lane == 0) NFI_BTRACE(3, it, 1);
       }
       __syncwarp();
       if (lane == 0) nfi_tc::mbar_arrive(&sm.meta_empty[m]);
     }
     flush();
-  } else {
-    // ------------------------------------------------------------------ MMA issuer: per-set state machine
-    // the whole warp polls (converged, uniform state); one elected lane issues MMAs, commits, arrives
-    uint32_t it0 = 0, it1 = 1, stage0 = 0, stage1 = 0, rph0 = 0, rph1 = 0, nact0 = 0, nact1 = 0;
-    uint32_t idle = 0;
-    auto step = [&](const int c, uint32_t& it, uint32_t& stage, uint32_t& rph, uint32_t& nact) -> bool {
-      if (it >= total) return false;
-      const uint32_t tacc = tmem + c * nfi_mlp::kTmemCols;
-      if (stage == 0) {
-        const uint32_t m = it % kBwNM;
-        if (!nfi_tc::mbar_test(&sm.meta_full[m], (it / kBwNM) & 1)) return false;
-        if (!nfi_tc::mbar_test(&sm.a_full[c], (it >> 1) & 1)) return false;
-        const int any = bw_any(sm.meta[m]);
-        if (any && nact > 0 && !nfi_tc::mbar_test(&sm.acc_free[c], (nact - 1) & 1)) return false;
-        __syncwarp();
-        if (!any) {
-          if (nfi_tc::elect_one()) { nfi_tc::mbar_arrive(&sm.meta_empty[m]); nfi_tc::mbar_arrive(&sm.a_empty[c]); }
-          it += 2;
-          return true;
-        }
+  } else if (warp < kMmaWarp) {
+    // ------------------------------------------------------------------ scatter: dF (+ T) -> gradients
+    const int sw = warp - kBwPS - kBwE;
+    const int row = sw * 32 + lane;
+    const uint32_t tl = tmem + ((uint32_t)(sw * 32) << 16);
+    const float inv_r = 1.f / a.f.scene_range;
+    float* sc = sm.dfe[sw];
+    uint32_t dfph[2] = {0, 0};
+    for (uint32_t it = 0; it < total; ++it) {
+      const uint32_t m = it % kBwNM, c = it & 1;
+      const int b = (int)(it / (uint32_t)ntile);
+      nfi_tc::mbar_wait(&sm.meta_full[m], (it / kBwNM) & 1);
+      const BwTable& tb = sm.tab[it % kBwNT];
+      const int sid = tb.sid[row];
+      const float keep = tb.keep[row];
+      const bool any = bw_any(sm.meta[m]) != 0;
+      float gp[3] = {0.f, 0.f, 0.f};
+      float g0[16], g1[16];
+      if (any) {
+        nfi_tc::mbar_wait(&sm.a_full[c], (it >> 1) & 1);          // T buffer c written (long ago)
+        nfi_tc::mbar_wait(&sm.df_full[c], dfph[c]); dfph[c] ^= 1;
+        if (sw == 0 && lane == 0) NFI_BTRACE(1, it, 0);
         nfi_tc::fence_after_sync();
-        if (nfi_tc::elect_one()) {
-          nfi_tc::mbar_arrive(&sm.meta_empty[m]);
-          nfi_mlp::issue_layer0_at(sm.w, sm.a[c][0], sm.a[c][1], tacc);
-          nfi_tc::mma_commit(&sm.a_empty[c]);
-          nfi_tc::mma_commit(&sm.acc_full[c]);
+        nfi_tc::tmem_ld16(tl + kBwColDF + 32 * c, g0);
+        nfi_tc::tmem_ld16(tl + kBwColDF + 32 * c + 16, g1);
+        nfi_tc::tmem_ld_wait();
+        if (WANT_PTS) {
+#pragma unroll
+          for (int k = 0; k < 3; ++k) {
+            float t0[16], t1[16];
+            nfi_tc::tmem_ld16(tl + kBwColT + 96 * c + 32 * k, t0);
+            nfi_tc::tmem_ld16(tl + kBwColT + 96 * c + 32 * k + 16, t1);
+            nfi_tc::tmem_ld_wait();
+            float s0 = 0.f, s1 = 0.f;
+#pragma unroll
+            for (int i = 0; i < 16; ++i) { s0 = fmaf(g0[i], t0[i], s0); s1 = fmaf(g1[i], t1[i], s1); }
+            gp[k] = keep >= 0.f ? (s0 + s1) * inv_r : 0.f;      // idle rows carry stale T
+          }
         }
-        __syncwarp();
-        if (lane == 0) NFI_BTRACE(4, it, 0);
-        ++nact; stage = 1;
-        return true;
+        nfi_tc::fence_before_sync();
       }
-      if (!nfi_tc::mbar_test(&sm.acc_ready[c], rph)) return false;
-      rph ^= 1;
+      __syncwarp();
+      if (lane == 0) nfi_tc::mbar_arrive(&sm.s_free[c]);
+      if (sw == 0 && lane == 0) NFI_BTRACE(1, it, 1);
+      if (WANT_PTS && keep != -1.f) {
+        float* dst = a.g_points + ((int64_t)b * per_image + sid) * 3;
+        dst[0] = gp[0]; dst[1] = gp[1]; dst[2] = gp[2];
+      }
+      if (any && a.g_planes) {
+#pragma unroll 1
+        for (int h = 0; h < 32 / kBwER; ++h) {          // kBwER rows through the warp's scratch at a time
+          __syncwarp();
+          if (lane / kBwER == h) {
+            float* dst = sc + (lane % kBwER) * kBwDfLd;
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+              *reinterpret_cast<float4*>(dst + 4 * i) = make_float4(g0[4 * i], g0[4 * i + 1], g0[4 * i + 2], g0[4 * i + 3]);
+              *reinterpret_cast<float4*>(dst + 16 + 4 * i) = make_float4(g1[4 * i], g1[4 * i + 1], g1[4 * i + 2], g1[4 * i + 3]);
+            }
+          }
+          __syncwarp();
+          bw_scatter_rows<kBwER>(a, tb, sc, b, sw * 32 + h * kBwER, lane);
+        }
+      }
+      if (sw == 0 && lane == 0) NFI_BTRACE(1, it, 2);
+      __syncwarp();
+      if (lane == 0) nfi_tc::mbar_arrive(&sm.meta_empty[m]);
+    }
+  } else {
+    // ------------------------------------------------------------------ MMA issuer
+    // the whole warp waits (converged); one elected lane issues the MMAs, commits and arrives
+    uint32_t rph = 0;
+    for (uint32_t it = 0; it < total; ++it) {
+      const uint32_t m = it % kBwNM, c = it & 1;
+      nfi_tc::mbar_wait(&sm.meta_full[m], (it / kBwNM) & 1);
+      nfi_tc::mbar_wait(&sm.a_full[c], (it >> 1) & 1);
+      const int any = bw_any(sm.meta[m]);
+      __syncwarp();
+      if (!any) {
+        if (nfi_tc::elect_one()) { nfi_tc::mbar_arrive(&sm.meta_empty[m]); nfi_tc::mbar_arrive(&sm.a_empty[c]); }
+        __syncwarp();
+        continue;
+      }
       nfi_tc::fence_after_sync();
-      if (stage == 1) {
-        if (nfi_tc::elect_one()) { nfi_mlp::issue_layer1_at(sm.w, tacc); nfi_tc::mma_commit(&sm.acc_full[c]); }
-        __syncwarp();
-        if (lane == 0) NFI_BTRACE(4, it, 1);
-        stage = 2;
-      } else if (stage == 2) {
-        if (nfi_tc::elect_one()) { nfi_mlp::issue_dh(sm.bw, tacc); nfi_tc::mma_commit(&sm.acc_full[c]); }
-        __syncwarp();
-        if (lane == 0) NFI_BTRACE(4, it, 2);
-        stage = 3;
-      } else {
-        if (nfi_tc::elect_one()) { nfi_mlp::issue_df(sm.bw, tacc); nfi_tc::mma_commit(&sm.df_full[c]); }
-        __syncwarp();
-        if (lane == 0) NFI_BTRACE(4, it, 3);
-        stage = 0; it += 2;
+      if (nfi_tc::elect_one()) {
+        nfi_tc::mbar_arrive(&sm.meta_empty[m]);
+        nfi_mlp::issue_layer0_at(sm.w, sm.a[c][0], sm.a[c][1], tmem);
+        nfi_tc::mma_commit(&sm.a_empty[c]);
+        nfi_tc::mma_commit(&sm.acc_full);
       }
-      return true;
-    };
-    while (it0 < total || it1 < total) {
-      const bool p0 = step(0, it0, stage0, rph0, nact0);
-      const bool p1 = step(1, it1, stage1, rph1, nact1);
-      if (p0 || p1) idle = 0;
-      else if (++idle > (1u << 26)) __trap();
+      __syncwarp();
+      if (lane == 0) NFI_BTRACE(4, it, 0);
+      nfi_tc::mbar_wait(&sm.acc_ready, rph); rph ^= 1;
+      nfi_tc::fence_after_sync();
+      if (nfi_tc::elect_one()) { nfi_mlp::issue_layer1_at(sm.w, tmem); nfi_tc::mma_commit(&sm.acc_full); }
+      __syncwarp();
+      if (lane == 0) NFI_BTRACE(4, it, 1);
+      nfi_tc::mbar_wait(&sm.acc_ready, rph); rph ^= 1;
+      nfi_tc::fence_after_sync();
+      if (nfi_tc::elect_one()) { nfi_mlp::issue_dh(sm.bw, tmem); nfi_tc::mma_commit(&sm.acc_full); }
+      __syncwarp();
+      if (lane == 0) NFI_BTRACE(4, it, 2);
+      nfi_tc::mbar_wait(&sm.acc_ready, rph); rph ^= 1;
+      nfi_tc::fence_after_sync();
+      if (nfi_tc::elect_one()) { nfi_mlp::issue_df(sm.bw, tmem, kBwColDF + 32 * c); nfi_tc::mma_commit(&sm.df_full[c]); }
+      __syncwarp();
+      if (lane == 0) NFI_BTRACE(4, it, 3);
     }
   }
   nfi_tc::fence_before_sync();
   __syncthreads();
-  if (warp == kBwPS + kBwE) nfi_tc::tmem_dealloc(tmem, 2 * nfi_mlp::kTmemCols);
+  if (warp == kMmaWarp) nfi_tc::tmem_dealloc(tmem, kBwTmemCols);
 }
 
 }  // namespace nfi_ftc

@@ -293,8 +293,8 @@ __device__ __forceinline__ void issue_dh(const BwdWeights& s, uint32_t tmem) {
   }
 }
 
-// dF <- dHpre . W0s   (24 MMAs, K = 64) -- ONE thread
-__device__ __forceinline__ void issue_df(const BwdWeights& s, uint32_t tmem) {
+// dF <- dHpre . W0s   (24 MMAs, K = 64) -- ONE thread; d_col = first of the 32 columns that receive dF
+__device__ __forceinline__ void issue_df(const BwdWeights& s, uint32_t tmem, uint32_t d_col = kColDF) {
   const uint32_t idesc = nfi_tc::idesc_tf32(kTile, kC);
   const uint32_t b_hi = nfi_tc::smem_u32(s.w0t_hi), b_lo = nfi_tc::smem_u32(s.w0t_lo);
   uint32_t acc = 0;
@@ -302,9 +302,9 @@ __device__ __forceinline__ void issue_df(const BwdWeights& s, uint32_t tmem) {
   for (int j = 0; j < kH / 8; ++j) {
     const uint64_t bh = nfi_tc::smem_desc(b_hi + 2 * j * kLboW0t, kLboW0t, kSBO);
     const uint64_t bl = nfi_tc::smem_desc(b_lo + 2 * j * kLboW0t, kLboW0t, kSBO);
-    nfi_tc::mma_tf32_ts(tmem + kColDF, tmem + kColHlo + 8 * j, bh, idesc, acc); acc = 1;
-    nfi_tc::mma_tf32_ts(tmem + kColDF, tmem + kColHhi + 8 * j, bl, idesc, 1);
-    nfi_tc::mma_tf32_ts(tmem + kColDF, tmem + kColHhi + 8 * j, bh, idesc, 1);
+    nfi_tc::mma_tf32_ts(tmem + d_col, tmem + kColHlo + 8 * j, bh, idesc, acc); acc = 1;
+    nfi_tc::mma_tf32_ts(tmem + d_col, tmem + kColHhi + 8 * j, bl, idesc, 1);
+    nfi_tc::mma_tf32_ts(tmem + d_col, tmem + kColHhi + 8 * j, bh, idesc, 1);
   }
 }
 
