@@ -229,8 +229,16 @@ def test_decoder_and_heads(nfi, name, A, use_sdf):
     leaves = [planes, pts] + ([pal] if A > 0 else []) + ([fld.beta, fld.alpha] if use_sdf else [])
     keys = ["ds_planes", "ds_pts"] + (["ds_palette"] if A > 0 else []) + (["ds_beta", "ds_alpha"] if use_sdf else [])
     gs = torch.autograd.grad((sigma * cu(g["gsigma"])).sum() + (rgb * cu(g["grgb"])).sum(), leaves)
+    # ds_alpha = -(1/alpha) * sum(gsigma * sigma) over random-sign gsigma is an ill-conditioned fp32 sum
+    # (sum|terms| / |sum| = 1.3e3 on this fixture), so the fp32 golden itself is only good to a few
+    # eps * sum|terms|; that floor is added to the contract tolerance for the two scalar reductions.
+    floor = 8 * 1.1920929e-07 * float((torch.as_tensor(g["sigma"]) * torch.as_tensor(g["gsigma"])).abs().sum())
     for a, k in zip(gs, keys):
-        assert rel_err(a.cpu(), g[k]) < TOL, k
+        if k in ("ds_alpha", "ds_beta"):
+            ref = torch.as_tensor(g[k]).double()
+            assert float((a.cpu().double() - ref).abs().max()) < TOL * float(ref.abs().max()) + floor, k
+        else:
+            assert rel_err(a.cpu(), g[k]) < TOL, k
 
 
 def test_sampler_dropin(nfi):
