@@ -242,6 +242,10 @@ def run_ours(args):
                      "field_fwd_share_of_step": (sum(fwd) / args.steps) / ms_step if ms_step else None},
     }
     if not args.no_cpu_baseline and world == 1:
+        try:                                  # reported baseline only: never fails the bench line
+            out["gpu_eager_baseline"] = gpu_eager_baseline(dev)
+        except Exception as e:                # noqa: BLE001
+            out["gpu_eager_baseline"] = {"unavailable": "%s: %s" % (type(e).__name__, str(e)[:200])}
         out["cpu_baseline"] = cpu_baseline(sample_res=args.cpu_res)
     elif world > 1:
         out["cpu_baseline"] = None
@@ -275,6 +279,44 @@ def cpu_step_fn(B, res):
         return float(loss)
 
     return step, B * H * W
+
+
+def gpu_eager_baseline(dev, B=2, res=128, steps=3):
+    """The reference's eager PyTorch path ON THE SAME GPU ("the kernel to beat"): the
+    oracle port executes the reference's own ATen ops (grid_sample, linear, softplus, cumprod, sort,
+    gather ...), TF32 off as run.py:59-60 sets it.  Bounded sample: B images of config 2 per step."""
+    import nfi_oracle as O
+    torch.backends.cuda.matmul.allow_tf32 = False
+    torch.backends.cudnn.allow_tf32 = False
+    H = W = res
+    S = 64
+    planes, fd, pal, cam, focal, target = [t.to(dev) if torch.is_tensor(t) else {k: v.to(dev) for k, v in t.items()}
+                                           for t in make_inputs(B, H, W, S)]
+    fp = O.FieldParams(fd["W0"], fd["b0"], fd["W1"], fd["b1"], SCENE_RANGE, True, 10, fd["beta"], fd["alpha"])
+
+    def step():
+        lv = [t.clone().requires_grad_() for t in (planes, pal, cam, focal)]
+        u_s = torch.rand(B, H, W, S, device=dev)
+        u_p = torch.rand(B * H * W, S, device=dev)
+        rgb, depth, mask = O.render(lv[0].view(B, 3, 32, 256, 256), lv[1], fp, H, W, lv[2], lv[3], None, None,
+                                    S, False, u_s, u_p)
+        loss = (rgb - target).abs().mean() * B
+        torch.autograd.grad(loss, lv)
+
+    step()
+    torch.cuda.synchronize(dev)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(steps):
+        step()
+    e1.record()
+    torch.cuda.synchronize(dev)
+    ms = e0.elapsed_time(e1) / steps
+    peak_gb = torch.cuda.max_memory_allocated(dev) / 2**30
+    return {"value": B * H * W / (ms * 1e-3), "unit": UNIT, "kind": "port", "ms_per_step": ms,
+            "sample": "oracle port of the reference PyTorch path run eagerly on this GPU (TF32 off): %d images "
+                      "%dx%d rays (64+64 samples), fwd+bwd, %d timed steps after 1 warm-up; peak %.1f GiB allocated"
+                      % (B, res, res, steps, peak_gb)}
 
 
 def cpu_baseline(sample_res=64):

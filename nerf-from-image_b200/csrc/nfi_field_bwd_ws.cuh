@@ -55,8 +55,12 @@ constexpr int kBwRed = 32;               // per-image scalar gradients reduced p
 constexpr int kBwColT = 240, kBwColDF = 432, kBwTmemCols = 512;
 
 __device__ __forceinline__ void red_add_v4(float* addr, float a, float b, float c, float d) {
+#ifdef NFI_EXP_STSCATTER   // developer A/B (tools/ab_build.py): plain stores, wrong results, timing only
+  asm volatile("st.global.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(addr), "f"(a), "f"(b), "f"(c), "f"(d) : "memory");
+#else
   asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(addr), "f"(a), "f"(b), "f"(c), "f"(d)
                : "memory");
+#endif
 }
 
 struct BwTable {                         // rows are written by the gather warp that owns them
@@ -185,6 +189,9 @@ __device__ __forceinline__ bool bw_phase1(const Args& a, BwTable& tb, const BwIn
 }
 
 __device__ __forceinline__ float4 bw_ldg(const char* base, uint32_t off) {
+#ifdef NFI_EXP_NOGATHER    // developer A/B: every sample reads texel 0 (L1 hits), timing only
+  off = 0;
+#endif
   return __ldg(reinterpret_cast<const float4*>(base + off));
 }
 __device__ __forceinline__ void bw_fma4(float4& acc, const float4& v, float w) {
@@ -582,7 +589,11 @@ field_bwd_ws_kernel(const Args a) {
         float* dst = a.g_points + ((int64_t)b * per_image + sid) * 3;
         dst[0] = gp[0]; dst[1] = gp[1]; dst[2] = gp[2];
       }
+#ifdef NFI_EXP_NOSCATTER
+      if (false) {
+#else
       if (any && a.g_planes) {
+#endif
 #pragma unroll 1
         for (int h = 0; h < 32 / kBwER; ++h) {          // kBwER rows through the warp's scratch at a time
           __syncwarp();

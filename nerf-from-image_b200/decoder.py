@@ -85,7 +85,7 @@ def triplanar_decoder_forward(self, xy, xz, yz, coords, requires_double_backward
 
 def make_sampler(planes, palette, field: Field, planes_layout: str = "nchw"):
     """Replacement for the `sampler` closure (models/generator.py:587-681) for the
-    ['sigma', 'rgb', 'semantics'] outputs.  `planes`: [B,96,Hp,Wp] / [B,3,32,Hp,Wp] (nchw) or
+    ['sdf_distance', 'sigma', 'rgb', 'normals', 'semantics', 'coords'] outputs.  `planes`: [B,96,Hp,Wp] / [B,3,32,Hp,Wp] (nchw) or
     [B,3,Hp,Wp,32] (cl)."""
     planes_cl = planes if planes_layout == "cl" else ops.planes_to_channels_last(planes)
 
@@ -95,9 +95,10 @@ def make_sampler(planes, palette, field: Field, planes_layout: str = "nchw"):
         bs = x_in.shape[0]
         pts = x_in.reshape(bs, -1, 3)
         out = {}
-        unsupported = [o for o in request_sampler_outputs if o in ("normals",)]
-        if unsupported:
-            raise NotImplementedError("nfi_b200 sampler: %s not covered yet (SURVEY.md 8(f) N1)" % unsupported)
+        want_nrm = "normals" in request_sampler_outputs
+        if want_nrm:                            # generator.py:599-602, 614-622: everything detached
+            assert field.cfg.use_sdf and torch.is_grad_enabled()
+            out["normals"] = ops.sdf_normals_on_points(planes_cl, *field.tensors()[:4], pts, field.cfg)
         if "sdf_distance" in request_sampler_outputs:
             y, _ = ops.field_on_points(planes_cl, None, *field.tensors(), pts, field.cfg, mode=1)
             out["sdf_distance"] = y[..., :1]
@@ -107,6 +108,8 @@ def make_sampler(planes, palette, field: Field, planes_layout: str = "nchw"):
         if want_sem or "sigma" in request_sampler_outputs or "rgb" in request_sampler_outputs:
             o4, probs = ops.field_on_points(planes_cl, palette, *field.tensors(), pts, field.cfg, mode=0,
                                             want_probs=want_sem)
+            if want_nrm:
+                o4 = o4.detach()
             if "sigma" in request_sampler_outputs:
                 out["sigma"] = o4[..., 0]
             if "rgb" in request_sampler_outputs:

@@ -317,6 +317,45 @@ def field_on_points(planes_cl, palette, W0, b0, W1, b1, beta, alpha, points, cfg
                         cfg, mode, 0, False, want_probs)
 
 
+def _sdf_normals(planes_cl, W0, b0, W1, b1, cfg, origins, dirs, z, points, img_w):
+    with torch.no_grad():
+        assert cfg.use_sdf, "normals need the SDF head (models/generator.py:600)"
+        pl = f32c(planes_cl)
+        B, _, Hp, Wp, _ = pl.shape
+        if points is None:
+            o, d, zz = f32c(origins.detach()), f32c(dirs.detach()), f32c(z.detach())
+            pts, S, lead = None, zz.shape[-1], zz.shape
+            npi = zz.numel() // S // B
+        else:
+            pts = f32c(points.detach())
+            o = d = zz = None
+            S, lead, npi = 1, pts.shape[:-1], pts.numel() // 3 // B
+        # raw-decoder mode: no heads, so the struct carries no beta / alpha
+        field, keep = _lib.make_field_struct(W0.detach(), b0.detach(), W1.detach(), b1.detach(), None, None,
+                                             cfg.attention_values, False, cfg.scene_range)
+        g = torch.zeros(*lead, field.n_out, dtype=torch.float32, device=pl.device)
+        g[..., 0] = 1.0
+        g_points = _empty(pl, *lead, 3)
+        call("nfi_field_bwd", pl, field, ptr(pl), None, B, Hp, Wp, ptr(o), ptr(d), ptr(zz), ptr(pts),
+             npi, S, 1, int(img_w), ptr(g), None, None, ptr(g_points), None, 0)
+        return torch.nn.functional.normalize(g_points, dim=-1)
+
+
+def sdf_normals_on_rays(planes_cl, W0, b0, W1, b1, origins, dirs, z, cfg, img_w=0):
+    """Unit SDF gradients at the samples o + d*z of every ray, [.., S, 3] -- the sampler's 'normals'
+    output (models/generator.py:599-602, 614-618: autograd of the distance channel wrt the query
+    points, then F.normalize).  Forward-only, as in the reference (it detaches everything in this
+    mode).  One launch of the fused field backward in raw-decoder mode with the upstream gradient
+    e_0 (distance channel) and no plane-gradient target: d y_0 / d point comes out of the same
+    tcgen05 chain (dY -> dH -> dF) and the bilinear tangents the pose gradient uses."""
+    return _sdf_normals(planes_cl, W0, b0, W1, b1, cfg, origins, dirs, z, None, img_w)
+
+
+def sdf_normals_on_points(planes_cl, W0, b0, W1, b1, points, cfg):
+    """Same at explicit world-space points [B, n, 3] -> [B, n, 3]."""
+    return _sdf_normals(planes_cl, W0, b0, W1, b1, cfg, None, None, None, points, 0)
+
+
 # ---------------------------------------------------------------------------------------------
 # A7 / A8  coarse weights, EG3D smoothing, inverse-CDF sampling (all under no_grad in the
 #          reference: run.py:261-281)

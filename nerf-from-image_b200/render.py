@@ -23,12 +23,16 @@ def render_planes(planes, palette, field: Field, height: int, width: int, tform_
                   randomize: bool = True, white_background: bool = False, fine_sampling: bool = True,
                   force_no_cam_grad: bool = False, zbuffer_depth: bool = False,
                   planes_layout: str = "nchw", u_strat=None, u_pdf=None, check_hits=True,
-                  return_aux: bool = False):
+                  return_aux: bool = False, compute_normals: bool = False,
+                  compute_semantics: bool = False, compute_coords: bool = False):
     """Render `B` images.  planes: [B,96,Hp,Wp] or [B,3,32,Hp,Wp] (layout 'nchw', the StyleGAN2
     output of models/generator.py:475-477) or [B,3,Hp,Wp,32] ('cl').  palette: attention values
     [B,A,3] (None for the plain RGB head).  Returns (rgb [B,H,W,3], depth [B,H,W], mask [B,H,W])
     (+ aux dict).  `u_strat` [B,H,W,S] / `u_pdf` [B*H*W,S] override the uniforms that are
-    otherwise drawn with torch.rand in the reference's order (nerf_utils.py:115, :204)."""
+    otherwise drawn with torch.rand in the reference's order (nerf_utils.py:115, :204).
+    compute_normals / compute_semantics / compute_coords (run.py:186-188) add the
+    forward-only maps aux["normals"] [B,H,W,3] and aux["semantics"] [B,H,W,A] (coords [B,H,W,3] take
+    the semantics slot, run.py:337-338); they imply `return_aux`."""
     H, W, S = int(height), int(width), int(depth_samples_per_ray)
     cam = tform_cam2world
     B = cam.shape[0]
@@ -46,26 +50,59 @@ def render_planes(planes, palette, field: Field, height: int, width: int, tform_
     planes_cl = planes if planes_layout == "cl" else ops.planes_to_channels_last(planes)
     wts = field.tensors()
     # A4-A6 on the coarse samples: (sigma, r, g, b) per sample
-    coarse, _ = ops.field_on_rays(planes_cl, palette, *wts, o_s, d_s, z_c, field.cfg, img_w=W,
-                                  skip_oob=True)
-    aux = {"origins": o, "dirs": d, "near": near, "far": far, "z_coarse": z_c}
+    extras = compute_normals or compute_semantics or compute_coords
+    want_sem = compute_semantics and not compute_coords
+    if compute_semantics:
+        assert field.cfg.attention_values > 0      # run.py:229
+    coarse, probs_c = ops.field_on_rays(planes_cl, palette, *wts, o_s, d_s, z_c, field.cfg, img_w=W,
+                                        skip_oob=not want_sem, want_probs=want_sem)
+    nrm_c = ops.sdf_normals_on_rays(planes_cl, *wts[:4], o_s, d_s, z_c, field.cfg, img_w=W) \
+        if compute_normals else None
+    aux = {"origins": o, "dirs": d, "near": near, "far": far, "z_coarse": z_c, "normals": None,
+           "semantics": None}
     if fine_sampling:
         # A7 + A8 (no_grad, run.py:261-281)
         if randomize and u_pdf is None:
             u_pdf = torch.rand((B * H * W, S), dtype=torch.float32, device=dev)
         z_f = ops.importance(coarse, d, z_c, u_pdf if randomize else None, sigma_stride=4)
-        fine, _ = ops.field_on_rays(planes_cl, palette, *wts, o_s, d_s, z_f, field.cfg, img_w=W,
-                                    skip_oob=True)
+        fine, probs_f = ops.field_on_rays(planes_cl, palette, *wts, o_s, d_s, z_f, field.cfg, img_w=W,
+                                          skip_oob=not want_sem, want_probs=want_sem)
         # A9 + A10
         rgb, depth, mask, perm, z_sorted = ops.merge_composite(
             coarse, fine, z_c, z_f, d, white_background, cam.detach() if zbuffer_depth else None)
         aux.update(z_fine=z_f, perm=perm, z_sorted=z_sorted)
+        if extras:
+            # N1: per-sample payloads in depth order (run.py:312-335) and their maps
+            # (nerf_utils.py:148-161); forward-only, from the stage-level compositing kernel
+            with torch.no_grad():
+                def sort(c, f):
+                    both = torch.cat((c, f), dim=-2)
+                    return both.gather(-2, perm.long().unsqueeze(-1).expand(*perm.shape, both.shape[-1]))
+                nrm = sem = None
+                if compute_normals:
+                    nrm_f = ops.sdf_normals_on_rays(planes_cl, *wts[:4], o_s, d_s, z_f, field.cfg, img_w=W)
+                    nrm = sort(nrm_c, nrm_f)
+                if compute_coords:
+                    sem = sort(ops.points_on_rays(o_s.detach(), d_s.detach(), z_c),
+                               ops.points_on_rays(o_s.detach(), d_s.detach(), z_f))
+                elif compute_semantics:
+                    sem = sort(probs_c, probs_f)
+                both = sort(coarse.detach(), fine.detach())
+                _, _, _, nmap, smap = ops.composite(both[..., 0], both[..., 1:], d.detach(), z_sorted, nrm,
+                                                    sem, white_background)
+                aux.update(normals=nmap, semantics=smap)
     else:
         rgb, depth, mask, _, _ = ops.composite(coarse[..., 0], coarse[..., 1:], d.detach(), z_c,
                                                None, None, white_background)
         if zbuffer_depth:
             raise NotImplementedError("z-buffer depth without fine sampling")
-    if return_aux:
+        if extras:
+            with torch.no_grad():
+                sem = ops.points_on_rays(o_s.detach(), d_s.detach(), z_c) if compute_coords else probs_c
+                _, _, _, nmap, smap = ops.composite(coarse[..., 0].detach(), coarse[..., 1:].detach(),
+                                                    d.detach(), z_c, nrm_c, sem, white_background)
+                aux.update(normals=nmap, semantics=smap)
+    if return_aux or extras:
         return rgb, depth, mask, aux
     return rgb, depth, mask
 
@@ -85,9 +122,8 @@ def make_render(args, dataset_config, zbuffer_depth: bool = False):
                force_no_cam_grad=False):
         if args.use_viewdir:
             raise NotImplementedError("nfi_b200.render: use_viewdir is not covered (SURVEY.md 8(f) N4)")
-        if compute_normals or compute_semantics or compute_coords:
-            raise NotImplementedError("nfi_b200.render: normals / semantics / coords outputs are not "
-                                      "covered yet (SURVEY.md 8(f) N1)")
+        if compute_normals:
+            assert args.use_sdf                    # run.py:226
         # The generator still produces planes and attention values (StyleGAN2 synthesis, out of
         # scope); the closure it returns holds them -- read them instead of calling it.
         model_outputs = target_model(None, model_input, ["sampler"] + list(extra_model_outputs),
@@ -99,11 +135,13 @@ def make_render(args, dataset_config, zbuffer_depth: bool = False):
         palette = cv.get("attention_values") if gen.attention_values > 0 else None
         field = Field.from_generator(gen)
         assert abs(float(gen.scene_range) - float(dataset_config["scene_range"])) < 1e-12
-        rgb, depth, mask = render_planes(
+        rgb, depth, mask, aux = render_planes(
             planes, palette, field, height, width, tform_cam2world, focal_length, center, bbox,
             depth_samples_per_ray, randomize=randomize,
             white_background=dataset_config["white_background"], fine_sampling=args.fine_sampling,
-            force_no_cam_grad=force_no_cam_grad, zbuffer_depth=zbuffer_depth)
-        return rgb, depth, mask, None, None, model_outputs
+            force_no_cam_grad=force_no_cam_grad, zbuffer_depth=zbuffer_depth, return_aux=True,
+            compute_normals=compute_normals, compute_semantics=compute_semantics,
+            compute_coords=compute_coords)
+        return rgb, depth, mask, aux["normals"], aux["semantics"], model_outputs
 
     return render

@@ -180,7 +180,7 @@ def golden_decoder():
         np.savez_compressed(os.path.join(OUT, "decoder_%s.npz" % name), **npy(out))
 
 
-def golden_render():
+def golden_render(only=()):
     """Whole `render` (run.py:176-350; eval_kitti_persp.py:43-230 for the z-buffer variant)."""
     cases = {
         # name: (script, persp, randomize, white, no_cam_grad, scene_range, H, W, center)
@@ -188,8 +188,16 @@ def golden_render():
         "ortho_det": ("run.py", False, False, False, False, 1.4, 12, 12, False),
         "persp_white_nocam": ("run.py", True, True, True, True, 1.4, 10, 14, False),
         "kitti_zbuf": ("eval_kitti_persp.py", True, True, True, False, 3.0, 12, 12, True),
+        # normals + semantics (the evaluation render, eval_kitti_persp.py:538-539)
+        # and coords (coord-regressor data synthesis, run.py:1639-1646); forward-only outputs
+        "persp_n1": ("run.py", True, True, True, False, 1.4, 12, 12, False),
+        "ortho_coords": ("run.py", False, True, False, False, 1.4, 12, 12, False),
     }
+    n1 = {"persp_n1": dict(compute_normals=True, compute_semantics=True),
+          "ortho_coords": dict(compute_coords=True)}
     for name, (script, persp, randomize, white, no_cam, sr, H, W, use_center) in cases.items():
+        if only and name not in only:
+            continue
         B, S, res = 2, 64, 16
         if name == "kitti_zbuf":
             B = 1
@@ -211,12 +219,25 @@ def golden_render():
         torch.manual_seed(77)
         out = render_ref(G, H, W, cam, focal, center, None, torch.zeros(B, 15, 512), S,
                          randomize=randomize, extra_model_inputs={"attention_values": palette},
-                         force_no_cam_grad=no_cam)
+                         force_no_cam_grad=no_cam, **n1.get(name, {}))
         torch.manual_seed(77)
         u1 = torch.rand(B, H, W, S) if randomize else None
         u2 = torch.rand(B * H * W, S) if randomize else None
         tgt = torch.rand(B, H, W, 3, generator=torch.Generator().manual_seed(8)) * 2 - 1
         gmask = torch.rand(B, H, W, generator=torch.Generator().manual_seed(9)) - 0.5
+        if name in n1:                       # forward-only fixtures
+            d = dict(planes=planes, palette=palette, cam=cam, focal=focal, center=center, u_strat=u1,
+                     u_pdf=u2, rgb=out[0], depth=out[1], mask=out[2], normals_map=out[3],
+                     semantics_map=out[4], **field)
+            d["meta"] = np.array([H, W, S, int(persp), int(randomize), int(white), int(no_cam),
+                                  int(script != "run.py")], dtype=np.int64)
+            d["scene_range"] = np.array(sr, dtype=np.float64)
+            d["flags"] = np.array([int(n1[name].get(k, False)) for k in
+                                   ("compute_normals", "compute_semantics", "compute_coords")], dtype=np.int64)
+            assert float(out[2].mean()) > 0.1, name
+            np.savez_compressed(os.path.join(OUT, "render_%s.npz" % name), **npy(d))
+            print(name, "mask mean %.3f" % float(out[2].mean()))
+            continue
         loss = (out[0] - tgt).abs().mean() * B + (out[2] * gmask).mean()
         wants = [planes, palette] + ([] if no_cam else ([cam] + ([focal] if persp else [])))
         gr = torch.autograd.grad(loss, wants, allow_unused=True)
@@ -238,8 +259,10 @@ def golden_render():
 if __name__ == "__main__":
     os.makedirs(OUT, exist_ok=True)
     torch.set_num_threads(4)
-    golden_functions()
-    golden_decoder()
-    golden_render()
+    only = tuple(a for a in sys.argv[1:] if not a.startswith("-"))   # e.g. `make_golden.py persp_n1`
+    if not only:
+        golden_functions()
+        golden_decoder()
+    golden_render(only)
     for f in sorted(os.listdir(OUT)):
         print(f, os.path.getsize(os.path.join(OUT, f)))

@@ -62,13 +62,13 @@ def aten_row_sum(x: torch.Tensor) -> torch.Tensor:
         for k in range(ILP):
             v = vec[r * ILP + k]
             part[k] = v if part[k] is None else part[k] + v
-    zero = torch.zeros(x.shape[:-1] + (V,), dtype=x.dtype)
+    zero = torch.zeros(x.shape[:-1] + (V,), dtype=x.dtype, device=x.device)
     part = [zero if p is None else p for p in part]
     for i in range(rows * ILP, nv):
         part[0] = part[0] + vec[i]
     for k in range(1, ILP):
         part[0] = part[0] + part[k]
-    acc = torch.zeros(x.shape[:-1], dtype=x.dtype)
+    acc = torch.zeros(x.shape[:-1], dtype=x.dtype, device=x.device)
     for k in range(nv * V, n):
         acc = acc + x[..., k]
     for k in range(V):
@@ -103,8 +103,9 @@ def pixel_rays(H: int, W: int, cam2world, focal=None, center=None, bbox=None):
     contract.  `bbox[b] = [[bx, by], [bw, bh]]`, `center[b] = [cx, cy]`.
     """
     B = cam2world.shape[0]
-    u = (torch.arange(W, dtype=torch.int64) / W).to(f32).view(1, 1, W).expand(1, H, W)
-    v = (torch.arange(H, dtype=torch.int64) / H).to(f32).view(1, H, 1).expand(1, H, W)
+    dev = cam2world.device                    # CPU is the pinned oracle; CUDA = the reference's eager GPU path
+    u = (torch.arange(W, dtype=torch.int64, device=dev) / W).to(f32).view(1, 1, W).expand(1, H, W)
+    v = (torch.arange(H, dtype=torch.int64, device=dev) / H).to(f32).view(1, H, 1).expand(1, H, W)
     R = cam2world[:, :3, :3]                  # [B,3,3]
     t = cam2world[:, :3, 3]                   # [B,3]
     if focal is not None:                     # nerf_utils.py:40-67
@@ -156,7 +157,7 @@ def box_near_far(o, d, scene_range: float, return_hit: bool = False):
     shape = o.shape[:-1]
     o = o.detach().reshape(-1, 3)
     d = d.detach().reshape(-1, 3)
-    r = torch.tensor(scene_range, dtype=f32)
+    r = torch.tensor(scene_range, dtype=f32, device=o.device)
     inv = 1 / d
     neg = inv < 0
     lo = torch.where(neg, r, -r)              # plane met first along the ray
@@ -195,7 +196,7 @@ def lerp_fma(a, b, w):
 
 def stratified_depths(near, far, S: int, u: Optional[torch.Tensor] = None):
     """z[..., k] = lerp(near, far, k/S) (+ u * (far-near)/S when jittered)."""
-    w = (torch.arange(S, dtype=torch.int64) / S).to(f32)
+    w = (torch.arange(S, dtype=torch.int64, device=near.device) / S).to(f32)
     z = lerp_fma(near.unsqueeze(-1), far.unsqueeze(-1), w)
     if u is not None:
         z = z + u * ((far - near).unsqueeze(-1) / S)
@@ -252,13 +253,23 @@ def decoder_mlp(feat, fp: FieldParams):
     return F.linear(h, fp.W1 * g1, fp.b1)
 
 
-def field_eval(planes, palette, pts, fp: FieldParams, want_probs: bool = False):
-    """pts [B,N,3] world units -> sigma [B,N], rgb [B,N,3] (+ attention probs [B,N,A])."""
+def field_eval(planes, palette, pts, fp: FieldParams, want_probs: bool = False, want_normals: bool = False):
+    """pts [B,N,3] world units -> sigma [B,N], rgb [B,N,3] (+ attention probs [B,N,A])
+    (+ unit SDF gradients [B,N,3] when `want_normals`; everything is then detached, generator.py:599-623)."""
+    if want_normals:                                                # generator.py:599-602
+        assert fp.use_sdf
+        pts = pts.detach().requires_grad_()
     x = pts / fp.scene_range                                        # generator.py:604
     with torch.no_grad():
         oob = (x.abs() > 1).any(dim=-1).to(f32)                     # generator.py:605-607
     y = decoder_mlp(triplane_features(planes, x), fp)
     dist, feats = y[..., 0], y[..., 1:]
+    normals = None
+    if want_normals:                                                # generator.py:614-623
+        with torch.enable_grad():
+            g, = torch.autograd.grad(dist.sum(), pts, create_graph=False)
+        normals = F.normalize(g, dim=-1)
+        dist, feats = dist.detach(), feats.detach()
     if fp.use_sdf:                                                  # generator.py:629-636
         t = -dist
         cdf = 0.5 + 0.5 * torch.sign(t) * (1 - torch.exp(-t.abs() / fp.beta))
@@ -271,6 +282,8 @@ def field_eval(planes, palette, pts, fp: FieldParams, want_probs: bool = False):
         rgb = torch.matmul(probs, palette)
     else:                                                           # generator.py:665-666
         rgb = torch.sigmoid(feats) * 2.004 - 1.002
+    if want_normals:
+        return sigma, rgb, probs, normals
     if want_probs:
         return sigma, rgb, probs
     return sigma, rgb
@@ -313,7 +326,7 @@ def inverse_cdf_samples(bins, weights, n: int, u: Optional[torch.Tensor] = None,
     pdf = w / aten_row_sum(w).unsqueeze(-1)
     cdf = torch.cat((torch.zeros_like(pdf[..., :1]), cumsum_f64(pdf)), dim=-1)      # [R,M]
     if u is None:
-        u = torch.linspace(0.0, 1.0, steps=n, dtype=w.dtype).expand(cdf.shape[0], n)
+        u = torch.linspace(0.0, 1.0, steps=n, dtype=w.dtype, device=w.device).expand(cdf.shape[0], n)
     u = u.contiguous()
     M = cdf.shape[-1]
     inds = (cdf.unsqueeze(1) <= u.unsqueeze(2)).sum(dim=-1)         # searchsorted(right=True)
@@ -374,8 +387,12 @@ def zbuffer_depth(depth, d_unit, cam2world):
 def render(planes, palette, fp: FieldParams, H: int, W: int, cam2world, focal=None, center=None,
            bbox=None, S: int = 64, white_background: bool = False, u_strat=None, u_pdf=None,
            randomize: bool = True, fine_sampling: bool = True, no_cam_grad: bool = False,
-           zbuffer: bool = False, want_semantics: bool = False, return_aux: bool = False):
-    """Full hot path.  `randomize=True` needs explicit uniforms u_strat [B,H,W,S], u_pdf [R,S]."""
+           zbuffer: bool = False, want_semantics: bool = False, return_aux: bool = False,
+           want_normals: bool = False, want_coords: bool = False):
+    """Full hot path.  `randomize=True` needs explicit uniforms u_strat [B,H,W,S], u_pdf [R,S].
+    `want_normals` / `want_semantics` / `want_coords` = compute_normals / compute_semantics /
+    compute_coords of run.py:186-188; the maps come back in aux["normals"], aux["semantics"] (coords
+    take the semantics slot, run.py:337-338)."""
     B = cam2world.shape[0]
     R = B * H * W
     o, d_raw = pixel_rays(H, W, cam2world, focal, center, bbox)
@@ -388,10 +405,13 @@ def render(planes, palette, fp: FieldParams, H: int, W: int, cam2world, focal=No
     if no_cam_grad:                                                  # run.py:211-214
         pts, d = pts.detach(), d.detach()
     dn = d.norm(p=2, dim=-1) if d.requires_grad else vec3_norm(d)
-    out = field_eval(planes, palette, pts.reshape(B, H * W * S, 3), fp, want_probs=True)
+    out = field_eval(planes, palette, pts.reshape(B, H * W * S, 3), fp, want_probs=True,
+                     want_normals=want_normals)
     sigma = out[0].view(B, H, W, S)
     rgb = out[1].view(B, H, W, S, 3)
     sem = out[2].view(B, H, W, S, -1) if (want_semantics and out[2] is not None) else None
+    nrm = out[3].view(B, H, W, S, 3) if want_normals else None
+    crd = pts.reshape(B, H, W, S, 3) if want_coords else None       # generator.py:644
     aux = {"origins": o, "dirs": d, "near": near, "far": far, "z_coarse": z_c}
     z_all = z_c
     if fine_sampling:
@@ -400,16 +420,25 @@ def render(planes, palette, fp: FieldParams, H: int, W: int, cam2world, focal=No
                                 (u_pdf if randomize else None)).view(B, H, W, S)
         z_all, perm = merge_depths(z_c, z_f)
         pts_f = points_on_rays(o, d, z_f) if not no_cam_grad else points_on_rays(o, d, z_f).detach()
-        out_f = field_eval(planes, palette, pts_f.reshape(B, H * W * S, 3), fp, want_probs=True)
+        out_f = field_eval(planes, palette, pts_f.reshape(B, H * W * S, 3), fp, want_probs=True,
+                           want_normals=want_normals)
         sigma = torch.cat((sigma, out_f[0].view(B, H, W, S)), dim=-1).gather(-1, perm)
         rgb = torch.cat((rgb, out_f[1].view(B, H, W, S, 3)), dim=-2).gather(
             -2, perm.unsqueeze(-1).expand(-1, -1, -1, -1, 3))
         if sem is not None:
             sem = torch.cat((sem, out_f[2].view(B, H, W, S, -1)), dim=-2).gather(
                 -2, perm.unsqueeze(-1).expand(-1, -1, -1, -1, sem.shape[-1]))
+        p3 = perm.unsqueeze(-1).expand(-1, -1, -1, -1, 3)
+        if nrm is not None:
+            nrm = torch.cat((nrm, out_f[3].view(B, H, W, S, 3)), dim=-2).gather(-2, p3)
+        if crd is not None:
+            crd = torch.cat((crd, pts_f.reshape(B, H, W, S, 3)), dim=-2).gather(-2, p3)
         aux.update(z_fine=z_f, perm=perm)
-    rgb_map, depth, mask, _, sem_map = composite(sigma, rgb, z_all, dn, white_background,
-                                                 semantics=sem)
+    if crd is not None:                                              # run.py:337-338
+        sem = crd
+    rgb_map, depth, mask, nrm_map, sem_map = composite(sigma, rgb, z_all, dn, white_background,
+                                                       normals=nrm, semantics=sem)
+    aux["normals"] = nrm_map
     if zbuffer:
         depth = zbuffer_depth(depth, d, cam2world)
     aux.update(z_sorted=z_all, semantics=sem_map)

@@ -42,3 +42,5 @@ def render_case(name):
 
 
 RENDER_CASES = ["persp_rand", "ortho_det", "persp_white_nocam", "kitti_zbuf"]
+# forward-only fixtures of the extra render outputs; g["flags"] = (normals, semantics, coords)
+N1_CASES = ["persp_n1", "ortho_coords"]
