@@ -129,6 +129,7 @@ class LaunchProfile:
 
 
 PROFILE = LaunchProfile()
+LAUNCHES = [0]            # kernels of this library launched so far by this process (always counted)
 
 
 def call(name, device_tensor, *args):
@@ -136,9 +137,10 @@ def call(name, device_tensor, *args):
     l = lib()
     with torch.cuda.device(device_tensor.device):
         ev = None
+        LAUNCHES[0] += KERNELS_PER_CALL.get(name, 1)
         if PROFILE.enabled:
             PROFILE.launches += KERNELS_PER_CALL.get(name, 1)
-            if name in PROFILE.timed:
+            if name in PROFILE.timed and not torch.cuda.is_current_stream_capturing():
                 ev = (torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True))
                 ev[0].record()
         rc = getattr(l, name)(*args, stream_of(device_tensor))

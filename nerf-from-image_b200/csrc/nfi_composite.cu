@@ -205,11 +205,64 @@ composite_bwd_kernel(const float* __restrict__ sigma, const float* __restrict__ 
 // A9 + A10 merged.  Rank-sort of the 2S depths in shared memory (stable: ties keep the
 // cat(coarse, fine) order), then the same scan as above on the permuted samples.
 // ------------------------------------------------------------------------------------------
-struct MergeSmem {
+struct alignas(16) MergeSmem {
   float zcat[128];
   float zs[128];
   uint8_t perm[128];
+  float zf_sorted[64];     // fast path scratch: the fine depths in ascending order
+  uint8_t chk[64];         // ... and who claimed each of their ranks (tie detection)
 };
+
+// number of leading elements of the ascending a[0..63] that satisfy (a[i] <= key) / (a[i] < key)
+template <bool LE>
+__device__ __forceinline__ int count_leading64(const float* a, float key) {
+  int pos = 0;
+#pragma unroll
+  for (int step = 64; step > 0; step >>= 1) {
+    const int q = pos + step;
+    const float v = a[q <= 64 ? q - 1 : 63];
+    const bool ok = q <= 64 && (LE ? v <= key : v < key);
+    pos = ok ? q : pos;
+  }
+  return pos;
+}
+
+// Ranks of the 64 coarse + 64 fine depths of one ray in the stable ascending order of
+// cat(coarse, fine) (run.py:283-285), without the 128 x 128 comparison: the coarse depths are
+// ascending by construction (stratified bins), so
+//   rank(coarse i) = i + #{fine < zc[i]},   rank(fine j) = #{coarse <= zf[j]} + rank of j among the fine,
+// the fine-among-fine ranks by a 64 x 64 strict comparison, the cross counts by binary search.
+// Returns false -- nothing written that matters -- when the coarse list is not ascending or two
+// fine depths are exactly equal; the caller then takes the general path.
+__device__ __forceinline__ bool merge_ranks_fast64(MergeSmem& m, int lane) {
+  const float2 c = reinterpret_cast<const float2*>(m.zcat)[lane];
+  const float2 f = reinterpret_cast<const float2*>(m.zcat + 64)[lane];
+  const float cnext = lane < 31 ? m.zcat[2 * lane + 2] : INFINITY;
+  if (!__all_sync(NFI_FULL, c.x <= c.y && c.y <= cnext)) return false;
+  int r0 = 0, r1 = 0;
+#pragma unroll
+  for (int k4 = 0; k4 < 16; ++k4) {
+    const float4 v = reinterpret_cast<const float4*>(m.zcat + 64)[k4];
+    r0 += (v.x < f.x) + (v.y < f.x) + (v.z < f.x) + (v.w < f.x);
+    r1 += (v.x < f.y) + (v.y < f.y) + (v.z < f.y) + (v.w < f.y);
+  }
+  const int j0 = 2 * lane, j1 = j0 + 1;
+  m.chk[r0] = (uint8_t)j0; m.zf_sorted[r0] = f.x;
+  __syncwarp();
+  m.chk[r1] = (uint8_t)j1; m.zf_sorted[r1] = f.y;
+  __syncwarp();
+  const bool distinct = m.chk[r0] == j0 && m.chk[r1] == j1 && r0 != r1;
+  if (!__all_sync(NFI_FULL, distinct)) return false;
+  const int rc0 = j0 + count_leading64<false>(m.zf_sorted, c.x);
+  const int rc1 = j1 + count_leading64<false>(m.zf_sorted, c.y);
+  const int rf0 = r0 + count_leading64<true>(m.zcat, f.x);
+  const int rf1 = r1 + count_leading64<true>(m.zcat, f.y);
+  m.zs[rc0] = c.x; m.perm[rc0] = (uint8_t)j0;
+  m.zs[rc1] = c.y; m.perm[rc1] = (uint8_t)j1;
+  m.zs[rf0] = f.x; m.perm[rf0] = (uint8_t)(64 + j0);
+  m.zs[rf1] = f.y; m.perm[rf1] = (uint8_t)(64 + j1);
+  return true;
+}
 
 __global__ void __launch_bounds__(kThreads)
 merge_composite_fwd_kernel(const float4* __restrict__ coarse, const float4* __restrict__ fine,
@@ -227,22 +280,24 @@ merge_composite_fwd_kernel(const float4* __restrict__ coarse, const float4* __re
     MergeSmem& m = sm[warp];
     for (int i = lane; i < S; i += 32) { m.zcat[i] = z_coarse[r * S + i]; m.zcat[S + i] = z_fine[r * S + i]; }
     __syncwarp();
-    float mine[E];
-    int rank[E];
+    if (!(S == 64 && merge_ranks_fast64(m, lane))) {     // general path: rank by comparison with all 2S
+      float mine[E];
+      int rank[E];
 #pragma unroll
-    for (int e = 0; e < E; ++e) { const int j = lane * E + e; mine[e] = j < n ? m.zcat[j] : INFINITY; rank[e] = 0; }
-    for (int k = 0; k < n; ++k) {
-      const float zk = m.zcat[k];
+      for (int e = 0; e < E; ++e) { const int j = lane * E + e; mine[e] = j < n ? m.zcat[j] : INFINITY; rank[e] = 0; }
+      for (int k = 0; k < n; ++k) {
+        const float zk = m.zcat[k];
+#pragma unroll
+        for (int e = 0; e < E; ++e) {
+          const int j = lane * E + e;
+          rank[e] += (zk < mine[e] || (zk == mine[e] && k < j)) ? 1 : 0;
+        }
+      }
 #pragma unroll
       for (int e = 0; e < E; ++e) {
         const int j = lane * E + e;
-        rank[e] += (zk < mine[e] || (zk == mine[e] && k < j)) ? 1 : 0;
+        if (j < n) { m.zs[rank[e]] = mine[e]; m.perm[rank[e]] = (uint8_t)j; }
       }
-    }
-#pragma unroll
-    for (int e = 0; e < E; ++e) {
-      const int j = lane * E + e;
-      if (j < n) { m.zs[rank[e]] = mine[e]; m.perm[rank[e]] = (uint8_t)j; }
     }
     __syncwarp();
     float sg[E], zz[E], gap[E], al[E], keep[E], T[E], w[E], col[E][3];

@@ -96,6 +96,18 @@ def near_far(origins, dirs, scene_range, check_hits=True):
     return near, far
 
 
+def count_launches():
+    """Kernels of this library launched so far (graph capture counts once: nfi_b200.graph)."""
+    return _lib.LAUNCHES[0]
+
+
+def take_pending_hits():
+    """Hand the deferred hit counters to a caller that resolves them itself (nfi_b200.graph)."""
+    pending = list(_PENDING_HITS)
+    del _PENDING_HITS[:]
+    return pending
+
+
 def raise_if_no_hits():
     """Resolve the deferred checks of near_far(check_hits="defer")."""
     if not _PENDING_HITS:
@@ -200,6 +212,29 @@ def _param_sizes(n_out):
     return [64 * 32, 64, n_out * 64, n_out, 1, 1]
 
 
+class PlaneGradSink:
+    """One plane-gradient buffer shared by the field passes of one render (coarse + fine read the same
+    planes).  Without it each pass zero-fills its own [B,3,Hp,Wp,32] gradient and autograd adds the
+    two -- 0.8 GB of fills and a 1.2 GB add per config-2 step.  With it the pass whose backward runs
+    first allocates the buffer and returns it as the gradient of `planes_cl`; the others accumulate
+    into it with the same atomics (stream-ordered, before the node that consumes it can run: autograd
+    keeps the first incoming gradient by reference and waits for every dependent) and return None.
+    State is per backward pass (`_current_graph_task_id`), so retained graphs and partial backwards
+    start from a fresh buffer."""
+
+    def __init__(self):
+        self.buf = None
+        self.task = None
+
+    def take(self, like):
+        """-> (buffer to accumulate into, gradient to return for planes_cl)"""
+        task = torch._C._current_graph_task_id()
+        if self.buf is not None and self.task == task and task != -1 and self.buf.shape == like.shape:
+            return self.buf, None
+        self.buf, self.task = torch.zeros_like(like), task
+        return self.buf, self.buf
+
+
 class _Field(Function):
     """inputs: planes_cl [B,3,Hp,Wp,32], palette [B,A,3]|None, W0,b0,W1,b1,beta,alpha,
     then EITHER (origins, dirs [B*npi,3], z [B*npi,S]) OR points [B,n,3].
@@ -207,7 +242,8 @@ class _Field(Function):
 
     @staticmethod
     def forward(ctx, planes_cl, palette, W0, b0, W1, b1, beta, alpha, origins, dirs, z, points,
-                cfg, mode, img_w, skip_oob, want_probs):
+                cfg, mode, img_w, skip_oob, want_probs, sink=None):
+        ctx.sink = sink
         pl = f32c(planes_cl)
         B, _, Hp, Wp, C = pl.shape
         assert C == 32 and pl.shape[1] == 3
@@ -255,7 +291,12 @@ class _Field(Function):
                                              cfg.use_sdf, cfg.scene_range)
         n_out = field.n_out
         g = f32c(g_out)
-        g_planes = torch.zeros_like(pl) if need[0] else None
+        g_planes = ret_planes = None
+        if need[0]:
+            if ctx.sink is not None:
+                g_planes, ret_planes = ctx.sink.take(pl)
+            else:
+                g_planes = ret_planes = torch.zeros_like(pl)
         g_pal = torch.zeros_like(pal) if (pal is not None and need[1] and mode == 0) else None
         want_pts = (need[8] or need[9]) if pts is None else need[11]
         g_points = _empty(pl, *g.shape[:-1], 3) if want_pts else None
@@ -287,8 +328,8 @@ class _Field(Function):
                 gb0 = g_params[o0:o1].view_as(b0) if need[3] else None
                 gW1 = g_params[o1:o2].view_as(W1) if need[4] else None
                 gb1 = g_params[o2:base].view_as(b1) if need[5] else None
-        return (g_planes, g_pal, gW0, gb0, gW1, gb1, g_beta, g_alpha, go, gd, None, gp,
-                None, None, None, None, None)
+        return (ret_planes, g_pal, gW0, gb0, gW1, gb1, g_beta, g_alpha, go, gd, None, gp,
+                None, None, None, None, None, None)
 
 
 def decoder_mlp(feat, W0, b0, W1, b1, want_hidden=False):
@@ -304,10 +345,11 @@ def decoder_mlp(feat, W0, b0, W1, b1, want_hidden=False):
 
 
 def field_on_rays(planes_cl, palette, W0, b0, W1, b1, beta, alpha, origins, dirs, z, cfg,
-                  img_w=0, skip_oob=False, want_probs=False):
-    """(sigma, r, g, b) [.., S, 4] for the samples o + d*z of every ray (no points tensor in HBM)."""
+                  img_w=0, skip_oob=False, want_probs=False, sink=None):
+    """(sigma, r, g, b) [.., S, 4] for the samples o + d*z of every ray (no points tensor in HBM).
+    `sink`: a PlaneGradSink shared with the other passes over the same planes_cl."""
     return _Field.apply(planes_cl, palette, W0, b0, W1, b1, beta, alpha, origins, dirs, z.detach(),
-                        None, cfg, 0, img_w, skip_oob, want_probs)
+                        None, cfg, 0, img_w, skip_oob, want_probs, sink)
 
 
 def field_on_points(planes_cl, palette, W0, b0, W1, b1, beta, alpha, points, cfg, mode=0,

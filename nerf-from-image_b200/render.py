@@ -54,8 +54,9 @@ def render_planes(planes, palette, field: Field, height: int, width: int, tform_
     want_sem = compute_semantics and not compute_coords
     if compute_semantics:
         assert field.cfg.attention_values > 0      # run.py:229
+    sink = ops.PlaneGradSink() if fine_sampling else None     # coarse + fine: one gradient buffer
     coarse, probs_c = ops.field_on_rays(planes_cl, palette, *wts, o_s, d_s, z_c, field.cfg, img_w=W,
-                                        skip_oob=not want_sem, want_probs=want_sem)
+                                        skip_oob=not want_sem, want_probs=want_sem, sink=sink)
     nrm_c = ops.sdf_normals_on_rays(planes_cl, *wts[:4], o_s, d_s, z_c, field.cfg, img_w=W) \
         if compute_normals else None
     aux = {"origins": o, "dirs": d, "near": near, "far": far, "z_coarse": z_c, "normals": None,
@@ -66,7 +67,7 @@ def render_planes(planes, palette, field: Field, height: int, width: int, tform_
             u_pdf = torch.rand((B * H * W, S), dtype=torch.float32, device=dev)
         z_f = ops.importance(coarse, d, z_c, u_pdf if randomize else None, sigma_stride=4)
         fine, probs_f = ops.field_on_rays(planes_cl, palette, *wts, o_s, d_s, z_f, field.cfg, img_w=W,
-                                          skip_oob=not want_sem, want_probs=want_sem)
+                                          skip_oob=not want_sem, want_probs=want_sem, sink=sink)
         # A9 + A10
         rgb, depth, mask, perm, z_sorted = ops.merge_composite(
             coarse, fine, z_c, z_f, d, white_background, cam.detach() if zbuffer_depth else None)
