@@ -308,9 +308,15 @@ merge_composite_fwd_kernel(const float4* __restrict__ coarse, const float4* __re
         const int src = m.perm[i];
         const float4 p = src < S ? coarse[r * S + src] : fine[r * S + (src - S)];
         sg[e] = p.x; col[e][0] = p.y; col[e][1] = p.z; col[e][2] = p.w; zz[e] = m.zs[i];
-        if (perm_out) perm_out[r * n + i] = (uint8_t)src;
-        if (z_sorted) z_sorted[r * n + i] = zz[e];
+        if (n != 32 * E) {
+          if (perm_out) perm_out[r * n + i] = (uint8_t)src;
+          if (z_sorted) z_sorted[r * n + i] = zz[e];
+        }
       } else { sg[e] = 0.f; col[e][0] = col[e][1] = col[e][2] = 0.f; zz[e] = 0.f; }
+    }
+    if (n == 32 * E) {                         // full rows: one 4-byte / 16-byte store per lane
+      if (perm_out) reinterpret_cast<uchar4*>(perm_out + r * n)[lane] = reinterpret_cast<const uchar4*>(m.perm)[lane];
+      if (z_sorted) reinterpret_cast<float4*>(z_sorted + r * n)[lane] = make_float4(zz[0], zz[1], zz[2], zz[3]);
     }
     const float d[3] = {dirs[r * 3], dirs[r * 3 + 1], dirs[r * 3 + 2]};
     nfi_warp_weights<E>(sg, zz, n, nfi_norm3(d), lane, gap, al, keep, T, w);
@@ -355,13 +361,19 @@ merge_composite_bwd_kernel(const float4* __restrict__ coarse, const float4* __re
   for (int64_t r = (int64_t)blockIdx.x * kWarps + warp; r < R; r += nwarps) {
     float sg[E], zz[E], gap[E], al[E], keep[E], T[E], w[E], col[E][3];
     int src[E];
+    if (n == 32 * E) {                         // full rows: one 4-byte / 16-byte load per lane
+      const uchar4 pp = reinterpret_cast<const uchar4*>(perm + r * n)[lane];
+      const float4 zv = reinterpret_cast<const float4*>(z_sorted + r * n)[lane];
+      src[0] = pp.x; src[1] = pp.y; src[2] = pp.z; src[3] = pp.w;
+      zz[0] = zv.x; zz[1] = zv.y; zz[2] = zv.z; zz[3] = zv.w;
+    }
 #pragma unroll
     for (int e = 0; e < E; ++e) {
       const int i = lane * E + e;
       if (i < n) {
-        src[e] = perm[r * n + i];
+        if (n != 32 * E) { src[e] = perm[r * n + i]; zz[e] = z_sorted[r * n + i]; }
         const float4 p = src[e] < S ? coarse[r * S + src[e]] : fine[r * S + (src[e] - S)];
-        sg[e] = p.x; col[e][0] = p.y; col[e][1] = p.z; col[e][2] = p.w; zz[e] = z_sorted[r * n + i];
+        sg[e] = p.x; col[e][0] = p.y; col[e][1] = p.z; col[e][2] = p.w;
       } else { src[e] = -1; sg[e] = 0.f; col[e][0] = col[e][1] = col[e][2] = 0.f; zz[e] = 0.f; }
     }
     const float d[3] = {dirs[r * 3], dirs[r * 3 + 1], dirs[r * 3 + 2]};
@@ -469,6 +481,8 @@ extern "C" int nfi_merge_composite_fwd(const float* coarse, const float* fine, c
   NFI_REQUIRE(R > 0 && S >= 1 && (!cam2world || rays_per_image > 0), NFI_ERR_BAD_ARG, "nfi_merge_composite_fwd: bad sizes");
   NFI_REQUIRE(S <= NFI_MAX_S, NFI_ERR_UNSUPPORTED, "nfi_merge_composite_fwd: S = %d > %d", S, NFI_MAX_S);
   NFI_REQUIRE(nfi_aligned16(coarse) && nfi_aligned16(fine), NFI_ERR_ALIGNMENT, "nfi_merge_composite_fwd: float4 buffers must be 16-byte aligned");
+  NFI_REQUIRE((!z_sorted || nfi_aligned16(z_sorted)) && (((uintptr_t)perm) & 3u) == 0, NFI_ERR_ALIGNMENT,
+              "nfi_merge_composite_fwd: z_sorted must be 16-byte and perm 4-byte aligned");
   merge_composite_fwd_kernel<<<warp_grid(R), kThreads, 0, nfi_cu(stream)>>>(
       (const float4*)coarse, (const float4*)fine, z_coarse, z_fine, dirs, R, S, white_background, cam2world,
       rays_per_image, rgb_map, depth_map, mask, perm, z_sorted);
@@ -487,6 +501,8 @@ extern "C" int nfi_merge_composite_bwd(const float* coarse, const float* fine, c
   NFI_REQUIRE(S <= NFI_MAX_S, NFI_ERR_UNSUPPORTED, "nfi_merge_composite_bwd: S = %d > %d", S, NFI_MAX_S);
   NFI_REQUIRE(nfi_aligned16(coarse) && nfi_aligned16(fine) && nfi_aligned16(g_coarse) && nfi_aligned16(g_fine),
               NFI_ERR_ALIGNMENT, "nfi_merge_composite_bwd: float4 buffers must be 16-byte aligned");
+  NFI_REQUIRE(nfi_aligned16(z_sorted) && (((uintptr_t)perm) & 3u) == 0, NFI_ERR_ALIGNMENT,
+              "nfi_merge_composite_bwd: z_sorted must be 16-byte and perm 4-byte aligned");
   merge_composite_bwd_kernel<<<warp_grid(R), kThreads, 0, nfi_cu(stream)>>>(
       (const float4*)coarse, (const float4*)fine, z_sorted, perm, dirs, R, S, white_background, g_rgb_map,
       g_mask, (float4*)g_coarse, (float4*)g_fine);

@@ -25,7 +25,7 @@
 //   meta_full[m]  gather -> everyone                 tables + activity flags of a tile written
 //   meta_empty[m] epilogue + scatter + MMA -> gather tile finished: its table slot may be rewritten
 //   a_full[c]     gather -> MMA                      F stage c and T buffer c written (or tile idle)
-//   a_empty[c]    MMA (commit) -> gather             layer 0 has read stage c
+//   a_empty       MMA (commit) -> gather             layer 0 has read the F stage
 //   acc_full      MMA (commit) -> epilogue           next accumulator of the chain is complete
 //   acc_ready     epilogue -> MMA                    next A operand (H, dY, dHpre) is in TMEM
 //   df_full[c]    MMA (commit) -> scatter            dF buffer c is complete
@@ -48,6 +48,12 @@ constexpr int kBwThreads = (kBwPS + kBwE + kBwS + 1) * 32;     // 544
 #endif
 constexpr int kBwNT = NFI_BW_RING;       // table ring: a slot is free once the tile has been scattered
 constexpr int kBwER = NFI_BW_EROWS;      // rows of dF a scatter warp stages at a time for its atomics
+#ifndef NFI_BW_ASTAGES
+#define NFI_BW_ASTAGES 2
+#endif
+constexpr int kBwNA = NFI_BW_ASTAGES;    // F operand stages.  Measured (round 1k): one stage would free 33 KB of shared
+                                         // memory for L1, but couples the gather to the MMA chain (layer 0 of tile it is
+                                         // only issued after the chain of tile it - 1): 7.8 ms per launch against 6.9
 constexpr int kBwNM = 8;                 // ring of activity flags (deeper: read by warps that lag)
 constexpr int kBwDfLd = 36;              // dF scratch row stride (floats)
 constexpr int kBwTLd = 100;              // T scratch row stride (floats): 96 + 4, conflict-free both ways
@@ -80,14 +86,14 @@ struct BwIn {                            // per warp: phase-1 inputs of its 16 r
 struct BwSmem {
   nfi_mlp::FwdWeights w;
   nfi_mlp::BwdWeights bw;
-  float a[2][2][nfi_mlp::kStageFloats];
+  float a[kBwNA][2][nfi_mlp::kStageFloats];
   BwTable tab[kBwNT];
   float tq[4][32 * kBwTLd];              // per lane quarter: T rows of the tile being gathered
   float dfe[kBwS][kBwER * kBwDfLd];
   BwMeta meta[kBwNM];
   float pal[kBwE][48];
   BwIn in[kBwPS];
-  uint64_t a_full[2], a_empty[2], df_full[2], s_free[2], acc_full, acc_ready;
+  uint64_t a_full[2], a_empty[kBwNA], df_full[2], s_free[2], acc_full, acc_ready;
   uint64_t meta_full[kBwNM], meta_empty[kBwNM];
   uint32_t tmem_base;
   uint32_t pad;
@@ -349,7 +355,7 @@ field_bwd_ws_kernel(const Args a) {
   nfi_mlp::load_weights_bwd(sm.bw, a.f.W0, a.f.W1, a.f.n_out);
   if (tid == 0) {
     for (int c = 0; c < 2; ++c) {
-      nfi_tc::mbar_init(&sm.a_full[c], kBwPS);  nfi_tc::mbar_init(&sm.a_empty[c], 1);
+      nfi_tc::mbar_init(&sm.a_full[c], kBwPS);  if (c < kBwNA) nfi_tc::mbar_init(&sm.a_empty[c], 1);
       nfi_tc::mbar_init(&sm.df_full[c], 1);     nfi_tc::mbar_init(&sm.s_free[c], kBwS);
     }
     nfi_tc::mbar_init(&sm.acc_full, 1);
@@ -401,11 +407,14 @@ field_bwd_ws_kernel(const Args a) {
       }
       if (w == 0 && lane == 0) NFI_BTRACE(0, it, 1);
       nfi_tc::mbar_wait(&sm.meta_full[m], (it / kBwNM) & 1);          // the flags of all eight warps
+      // layer 0 of the previous user of this F stage has read it.  Waited for on idle tiles too: every tile
+      // completes one phase of the barrier, so the parity test is only sound one phase behind
+      const uint32_t ca = kBwNA == 2 ? c : 0u;
+      nfi_tc::mbar_wait(&sm.a_empty[ca], (((kBwNA == 2 ? it >> 1 : it)) & 1) ^ 1);
       if (bw_any(sm.meta[m])) {
-        nfi_tc::mbar_wait(&sm.a_empty[c], ((it >> 1) & 1) ^ 1);       // layer 0 of tile it - 2 has read stage c
         if (it >= 2) nfi_tc::mbar_wait(&sm.s_free[c], ((it >> 1) - 1) & 1);   // T / dF buffers c read
         if (w == 0 && lane == 0) NFI_BTRACE(0, it, 2);
-        bw_gather<WANT_PTS>(a, tb, sm.a[c][0], sm.a[c][1], sm.tq[q], b, w, lane);
+        bw_gather<WANT_PTS>(a, tb, sm.a[ca][0], sm.a[ca][1], sm.tq[q], b, w, lane);
         if (WANT_PTS) {
           nfi_tc::named_bar_sync(1 + q, 64);             // both halves of the quarter are in the scratch
           bw_store_t(sm.tq[q], tmem + lane_off + kBwColT + 96 * c, half, lane);
@@ -624,15 +633,16 @@ field_bwd_ws_kernel(const Args a) {
       const int any = bw_any(sm.meta[m]);
       __syncwarp();
       if (!any) {
-        if (nfi_tc::elect_one()) { nfi_tc::mbar_arrive(&sm.meta_empty[m]); nfi_tc::mbar_arrive(&sm.a_empty[c]); }
+        if (nfi_tc::elect_one()) { nfi_tc::mbar_arrive(&sm.meta_empty[m]); nfi_tc::mbar_arrive(&sm.a_empty[kBwNA == 2 ? c : 0u]); }
         __syncwarp();
         continue;
       }
       nfi_tc::fence_after_sync();
       if (nfi_tc::elect_one()) {
         nfi_tc::mbar_arrive(&sm.meta_empty[m]);
-        nfi_mlp::issue_layer0_at(sm.w, sm.a[c][0], sm.a[c][1], tmem);
-        nfi_tc::mma_commit(&sm.a_empty[c]);
+        const uint32_t ca = kBwNA == 2 ? c : 0u;
+        nfi_mlp::issue_layer0_at(sm.w, sm.a[ca][0], sm.a[ca][1], tmem);
+        nfi_tc::mma_commit(&sm.a_empty[ca]);
         nfi_tc::mma_commit(&sm.acc_full);
       }
       __syncwarp();

@@ -39,6 +39,48 @@ plane_transpose_kernel(const float* __restrict__ src, float* __restrict__ dst, i
   }
 }
 
+// Same transposition with one 16-byte global access per thread on both sides (HW % 128 == 0, Wp % 4 == 0):
+// a block moves four 32-texel x 32-channel tiles; NCHW side: thread (c, x4) takes 4 consecutive texels
+// of channel c; channels-last side: thread (p, c4) takes 4 consecutive channels of texel p (8 lanes =
+// one 128-byte texel).  The padded tile makes all four scalar shared-memory accesses conflict-free.
+template <bool TO_CL>
+__global__ void __launch_bounds__(256)
+plane_transpose4_kernel(const float* __restrict__ src, float* __restrict__ dst, int HW, int Wp, int bshift) {
+  __shared__ float tile[32][33];
+  const int64_t plane = blockIdx.y;
+  const float* s = src + plane * 32 * (int64_t)HW;
+  float* d = dst + plane * 32 * (int64_t)HW;
+  const int t = threadIdx.x;
+  const int c = t >> 3, x4 = (t & 7) * 4;          // NCHW side
+  const int p = t >> 3, c4 = (t & 7) * 4;          // channels-last side
+#pragma unroll 1
+  for (int k = 0; k < 4; ++k) {
+    const int p0 = (blockIdx.x * 4 + k) * 32;
+    if (TO_CL) {
+      const float4 v = *reinterpret_cast<const float4*>(s + (int64_t)c * HW + p0 + x4);
+      tile[c][x4] = v.x; tile[c][x4 + 1] = v.y; tile[c][x4 + 2] = v.z; tile[c][x4 + 3] = v.w;
+      __syncthreads();
+      *reinterpret_cast<float4*>(d + (int64_t)texel_index(p0 + p, Wp, bshift) * 32 + c4) =
+          make_float4(tile[c4][p], tile[c4 + 1][p], tile[c4 + 2][p], tile[c4 + 3][p]);
+    } else {
+      const float4 v = *reinterpret_cast<const float4*>(s + (int64_t)texel_index(p0 + p, Wp, bshift) * 32 + c4);
+      tile[c4][p] = v.x; tile[c4 + 1][p] = v.y; tile[c4 + 2][p] = v.z; tile[c4 + 3][p] = v.w;
+      __syncthreads();
+      *reinterpret_cast<float4*>(d + (int64_t)c * HW + p0 + x4) =
+          make_float4(tile[c][x4], tile[c][x4 + 1], tile[c][x4 + 2], tile[c][x4 + 3]);
+    }
+    __syncthreads();
+  }
+}
+
+template <bool TO_CL>
+void launch_plane_transpose(const float* src, float* dst, int B, int HW, int Wp, int bshift, cudaStream_t st) {
+  if (HW % 128 == 0 && Wp % 4 == 0 && nfi_aligned16(src) && nfi_aligned16(dst))
+    plane_transpose4_kernel<TO_CL><<<dim3(HW / 128, B * 3), 256, 0, st>>>(src, dst, HW, Wp, bshift);
+  else
+    plane_transpose_kernel<TO_CL><<<dim3((HW + 31) / 32, B * 3), 256, 0, st>>>(src, dst, HW, Wp, bshift);
+}
+
 template <typename K>
 int set_smem(K kernel, int bytes, const char* who) {
   cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
@@ -52,7 +94,7 @@ extern "C" int nfi_planes_to_cl(const float* planes_nchw, int B, int Hp, int Wp,
                                 nfi_stream_t stream) {
   NFI_REQUIRE(planes_nchw && planes_cl && B > 0 && Hp > 0 && Wp > 0, NFI_ERR_BAD_ARG, "nfi_planes_to_cl: bad argument");
   const int HW = Hp * Wp;
-  plane_transpose_kernel<true><<<dim3((HW + 31) / 32, B * 3), 256, 0, nfi_cu(stream)>>>(planes_nchw, planes_cl, HW, Wp, nfi_plane_bshift(Hp, Wp));
+  launch_plane_transpose<true>(planes_nchw, planes_cl, B, HW, Wp, nfi_plane_bshift(Hp, Wp), nfi_cu(stream));
   NFI_CHECK_LAUNCH("plane_transpose_kernel<to_cl>");
   return NFI_OK;
 }
@@ -61,7 +103,7 @@ extern "C" int nfi_planes_grad_from_cl(const float* g_planes_cl, int B, int Hp, 
                                        float* g_planes_nchw, nfi_stream_t stream) {
   NFI_REQUIRE(g_planes_cl && g_planes_nchw && B > 0 && Hp > 0 && Wp > 0, NFI_ERR_BAD_ARG, "nfi_planes_grad_from_cl: bad argument");
   const int HW = Hp * Wp;
-  plane_transpose_kernel<false><<<dim3((HW + 31) / 32, B * 3), 256, 0, nfi_cu(stream)>>>(g_planes_cl, g_planes_nchw, HW, Wp, nfi_plane_bshift(Hp, Wp));
+  launch_plane_transpose<false>(g_planes_cl, g_planes_nchw, B, HW, Wp, nfi_plane_bshift(Hp, Wp), nfi_cu(stream));
   NFI_CHECK_LAUNCH("plane_transpose_kernel<from_cl>");
   return NFI_OK;
 }

@@ -5,7 +5,7 @@ rows = list(csv.reader(open(sys.argv[1])))
 hi = [i for i, r in enumerate(rows) if 'Kernel Name' in r][0]
 h = rows[hi]; kn = h.index('Kernel Name'); mv = h.index('Metric Value')
 seq = [(r[kn], float(r[mv].replace(',', '')) / 1e3) for r in rows[hi + 1:] if len(r) > mv]
-starts = [i for i, (k, v) in enumerate(seq) if 'plane_transpose_kernel<1>' in k]
+starts = [i for i, (k, v) in enumerate(seq) if 'plane_transpose' in k and '<1>' in k]
 n = int(sys.argv[2]) if len(sys.argv) > 2 else 3
 a, b = starts[n], starts[n + 1]
 tot = sum(v for _, v in seq[a:b])
