@@ -18,6 +18,7 @@
 #ifndef NFI_B200_H
 #define NFI_B200_H
 
+#include <stddef.h>
 #include <stdint.h>
 
 #ifdef __cplusplus
@@ -169,6 +170,48 @@ int nfi_merge_composite_bwd(const float* coarse, const float* fine, const float*
                             const uint8_t* perm, const float* dirs, int64_t R, int S,
                             int white_background, const float* g_rgb_map, const float* g_mask,
                             float* g_coarse, float* g_fine, nfi_stream_t stream);
+
+/* ---- A11 / A12: the whole render (run.py:176-350) and its backward as ONE pair of calls ----------
+ * Sequences A1-A10 above on `stream` inside a caller-owned workspace (nothing is allocated, nothing
+ * synchronises).  Ray r = (b*H + h)*W + w.  planes_cl: see nfi_planes_to_cl.  focal NULL = orthographic,
+ * focal_stride 0 = one shared focal (eval_kitti_persp.py:948).  randomize != 0: stratified jitter and
+ * random inverse-CDF uniforms, read from u_strat [R,S] / u_pdf [R,S] when given, else drawn in-kernel
+ * with Philox4x32-10 from (seed, offset); randomize == 0: the reference's deterministic linspace.
+ * Fine sampling is always on (arguments.py:124-127 default); S % 4 == 0, S <= NFI_MAX_S.
+ * After the forward (stream order) ((int32_t*)workspace)[0] = number of rays that hit the scene box;
+ * 0 is the case in which the reference raises (lib/nerf_utils.py:260). */
+typedef struct NfiRender {
+  NfiField field;
+  const float* planes_cl;   /* [B,3,Hp*Wp,32] */
+  const float* palette;     /* [B,A,3] attention values, NULL when field.attention_values == 0 */
+  const float* cam2world;   /* [B,16] */
+  const float* focal;       /* [B] / [1] / NULL */
+  const float* center;      /* [B,2] or NULL */
+  const float* bbox;        /* [B,2,2] or NULL */
+  const float* u_strat;     /* [R,S] or NULL */
+  const float* u_pdf;       /* [R,S] or NULL */
+  uint64_t seed, offset;
+  int32_t B, H, W, S, Hp, Wp;
+  int32_t focal_stride;
+  int32_t randomize;
+  int32_t white_background; /* dataset_config['white_background'] (lib/nerf_utils.py:158-161) */
+  int32_t zbuffer_depth;    /* eval_kitti_persp.py:221-228 */
+} NfiRender;
+
+/* bytes of workspace nfi_render_fwd needs (with_backward == 0) or fwd + bwd share (!= 0); 256-byte
+ * aligned base required.  0 on a malformed parameter block. */
+size_t nfi_render_workspace_bytes(const NfiRender* p, int with_backward);
+/* rgb [R,3], depth [R], mask [R]. */
+int nfi_render_fwd(const NfiRender* p, void* workspace, float* rgb, float* depth, float* mask,
+                   nfi_stream_t stream);
+/* `workspace` as left by nfi_render_fwd with the same `p`.  g_rgb [R,3], g_mask [R] or NULL.
+ * ACCUMULATING outputs (caller zero-fills; NULL = not wanted): g_planes_cl, g_palette [B,A,3],
+ * g_params (layout of nfi_field_bwd).  OVERWRITTEN: g_cam2world [B,16] and g_focal [B] (zeros for
+ * orthographic cameras) -- pass both for pose gradients, both NULL to skip them (force_no_cam_grad,
+ * run.py:211-214). */
+int nfi_render_bwd(const NfiRender* p, void* workspace, const float* g_rgb, const float* g_mask,
+                   float* g_planes_cl, float* g_palette, float* g_cam2world, float* g_focal,
+                   float* g_params, int want_weight_grads, nfi_stream_t stream);
 
 #ifdef __cplusplus
 }

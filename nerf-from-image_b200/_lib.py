@@ -29,8 +29,20 @@ class NfiField(Structure):
                 ("attention_values", c_int32), ("use_sdf", c_int32), ("scene_range", c_float)]
 
 
+class NfiRender(Structure):
+    """Mirror of `struct NfiRender` in include/nfi_b200.h."""
+    _fields_ = [("field", NfiField), ("planes_cl", c_void_p), ("palette", c_void_p), ("cam2world", c_void_p),
+                ("focal", c_void_p), ("center", c_void_p), ("bbox", c_void_p), ("u_strat", c_void_p),
+                ("u_pdf", c_void_p), ("seed", c_uint64), ("offset", c_uint64), ("B", c_int32), ("H", c_int32),
+                ("W", c_int32), ("S", c_int32), ("Hp", c_int32), ("Wp", c_int32), ("focal_stride", c_int32),
+                ("randomize", c_int32), ("white_background", c_int32), ("zbuffer_depth", c_int32)]
+
+
 _P = c_void_p
 _SIGS = {
+    "nfi_render_workspace_bytes": (ctypes.c_size_t, [POINTER(NfiRender), c_int]),
+    "nfi_render_fwd": (c_int, [POINTER(NfiRender), _P, _P, _P, _P, _P]),
+    "nfi_render_bwd": (c_int, [POINTER(NfiRender), _P, _P, _P, _P, _P, _P, _P, _P, c_int, _P]),
     "nfi_version": (c_int, []),
     "nfi_last_error": (c_char_p, []),
     "nfi_ray_bundle_fwd": (c_int, [_P, _P, c_int, _P, _P, c_int, c_int, c_int, c_int, _P, _P, _P]),

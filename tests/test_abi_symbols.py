@@ -13,7 +13,7 @@ HEADER = os.path.join(ROOT, "include", "nfi_b200.h")
 def _declared():
     src = open(HEADER).read()
     src = re.sub(r"/\*.*?\*/", "", src, flags=re.S)
-    return sorted(set(re.findall(r"^\s*(?:int|const char\s*\*)\s*(nfi_[a-z0-9_]+)\s*\(", src, flags=re.M)))
+    return sorted(set(re.findall(r"^\s*(?:int|size_t|const char\s*\*)\s*(nfi_[a-z0-9_]+)\s*\(", src, flags=re.M)))
 
 
 def test_header_declares_every_bound_symbol():

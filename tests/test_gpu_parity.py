@@ -477,3 +477,98 @@ def test_sampler_normals_vs_oracle(nfi):
     ln = n1.norm(dim=-1)
     assert bool((((ln - 1).abs() < 1e-5) | (ln == 0)).all())
     assert rel_err(n1, nrm0) < NORMALS_TOL
+
+
+# ---------------------------------------------------------------- fused C-ABI render, CUDA graph
+def _crender_case(nfi, B=2, HW=32, perspective=True, white=False, seed=21):
+    from nfi_b200 import synth
+    H = W = HW
+    S, res = 64, 64
+    planes = synth.make_planes(B, res=res, seed=1 + seed)
+    fd = synth.make_field(planes, seed=3 + seed)
+    pal = synth.make_palette(B, 10, seed=4 + seed)
+    cam, focal = synth.make_cameras(B, seed=2 + seed, perspective=perspective)
+    g = torch.Generator().manual_seed(seed)
+    u_s, u_p = torch.rand(B, H, W, S, generator=g).cuda(), torch.rand(B * H * W, S, generator=g).cuda()
+    target = (torch.rand(B, H, W, 3, generator=g) * 2 - 1).cuda()
+    gmask = (torch.rand(B, H, W, generator=g) - 0.5).cuda()
+    fld = nfi.dec.Field(*[fd[k].cuda() for k in ("W0", "b0", "W1", "b1", "beta", "alpha")], 1.4, 10, True)
+    return dict(B=B, H=H, W=W, S=S, planes=planes.cuda(), pal=pal.cuda(), cam=cam.cuda(),
+                focal=focal.cuda() if perspective else None, u_s=u_s, u_p=u_p, target=target, gmask=gmask,
+                fld=fld, white=white)
+
+
+@pytest.mark.parametrize("perspective,white", [(True, False), (False, True)])
+def test_fused_c_render_matches_autograd_path(nfi, perspective, white):
+    """nfi_render_fwd / nfi_render_bwd (one C call each, one workspace) against render_planes + autograd:
+    the same kernels in the same order, so images are bit-identical; gradients differ only by the order
+    of the fp32 atomics."""
+    from nfi_b200 import crender
+    c = _crender_case(nfi, perspective=perspective, white=white)
+    lv = [t.clone().requires_grad_() for t in (c["planes"], c["pal"], c["cam"])] + \
+         ([c["focal"].clone().requires_grad_()] if perspective else [])
+    focal = lv[3] if perspective else None
+    rgb, depth, mask = nfi.render.render_planes(lv[0], lv[1], c["fld"], c["H"], c["W"], lv[2], focal, None, None,
+                                                c["S"], randomize=True, white_background=white,
+                                                u_strat=c["u_s"], u_pdf=c["u_p"])
+    loss = ((rgb - c["target"]).abs().sum() + (mask * c["gmask"]).sum())
+    g_rgb, g_mask = torch.autograd.grad(loss, [rgb, mask], retain_graph=True)
+    grads = torch.autograd.grad(loss, lv)
+    pcl = nfi.ops.planes_to_channels_last(c["planes"])
+    cr = crender.CRender(pcl, c["pal"], c["fld"], c["H"], c["W"], c["cam"], c["focal"], None, None, c["S"],
+                         randomize=True, white_background=white, u_strat=c["u_s"], u_pdf=c["u_p"])
+    rgb2, depth2, mask2 = cr.forward()
+    assert torch.equal(rgb2, rgb.detach()) and torch.equal(depth2, depth) and torch.equal(mask2, mask.detach())
+    out = cr.backward(g_rgb, g_mask)
+    g_planes_cl = nfi.ops.planes_to_channels_last(grads[0])         # same layout as the C path's output
+    assert rel_err(out["planes_cl"].cpu(), g_planes_cl.cpu()) < 1e-5
+    assert rel_err(out["palette"].cpu(), grads[1].cpu()) < 1e-5
+    assert rel_err(out["cam2world"].cpu(), grads[2].cpu()) < 1e-5
+    if perspective:
+        assert rel_err(out["focal"].cpu(), grads[3].cpu()) < 1e-5
+
+
+def test_fused_c_render_philox_and_errors(nfi):
+    """No uniforms supplied: both passes draw Philox numbers from (seed, offset) -- reproducible per seed,
+    different across seeds, image statistics close to the torch.rand render; malformed calls come back as
+    NfiError with the library's message."""
+    from nfi_b200 import crender, _lib
+    c = _crender_case(nfi, B=2, HW=32)
+    pcl = nfi.ops.planes_to_channels_last(c["planes"])
+    mk = lambda seed: crender.CRender(pcl, c["pal"], c["fld"], c["H"], c["W"], c["cam"], c["focal"], None, None,
+                                      c["S"], randomize=True, seed=seed, with_backward=False).forward()
+    a, b, d = mk(7), mk(7), mk(8)
+    assert torch.equal(a[0], b[0]) and not torch.equal(a[0], d[0])
+    ref = nfi.render.render_planes(c["planes"], c["pal"], c["fld"], c["H"], c["W"], c["cam"], c["focal"], None, None,
+                                   c["S"], randomize=True, u_strat=c["u_s"], u_pdf=c["u_p"])
+    assert abs(float(a[2].mean()) - float(ref[2].mean())) < 0.02
+    assert float((a[0] - ref[0]).abs().mean()) < 0.05
+    with pytest.raises(_lib.NfiError):
+        crender.CRender(pcl, None, c["fld"], c["H"], c["W"], c["cam"], c["focal"], None, None, c["S"]).forward()
+
+
+def test_graphed_step_matches_eager(nfi):
+    """nfi_b200.graph.GraphedStep: the captured render forward + loss + backward replays to the eager
+    results, and new input values are picked up from the static buffers."""
+    from nfi_b200 import graph
+    c = _crender_case(nfi, B=2, HW=32)
+
+    def step(planes, pal, cam, focal, target):
+        rgb, depth, mask = nfi.render.render_planes(planes, pal, c["fld"], c["H"], c["W"], cam, focal, None, None,
+                                                    c["S"], randomize=True, u_strat=c["u_s"], u_pdf=c["u_p"],
+                                                    check_hits="defer")
+        loss = (rgb - target).abs().mean()
+        return (loss, rgb, *torch.autograd.grad(loss, [planes, pal, cam, focal]))
+
+    leaves = [t.clone().requires_grad_() for t in (c["planes"], c["pal"], c["cam"], c["focal"])] + [c["target"]]
+    gs = graph.GraphedStep(step, leaves)
+    for trial in range(2):
+        if trial == 1:      # perturbed inputs go through the same graph
+            leaves = [(t.detach() * 1.01).requires_grad_(t.requires_grad) for t in leaves]
+        ref = step(*leaves)
+        out = gs(*leaves)
+        gs.check_hits()
+        assert torch.equal(out[0], ref[0].detach()) and torch.equal(out[1], ref[1].detach())
+        for a, b in zip(out[2:], ref[2:]):
+            assert rel_err(a.cpu(), b.cpu()) < 1e-5
+    assert gs.launches_per_replay == 16
