@@ -572,3 +572,34 @@ def test_graphed_step_matches_eager(nfi):
         for a, b in zip(out[2:], ref[2:]):
             assert rel_err(a.cpu(), b.cpu()) < 1e-5
     assert gs.launches_per_replay == 16
+
+
+# ---------------------------------------------------------------- the paths the fast kernels fall back from
+@pytest.mark.parametrize("B,H,W,S,res", [
+    (1, 10, 14, 32, 20),     # ragged image (linear tile order), row-major texels (res % 8 != 0), general merge
+    (2, 8, 16, 30, 24),      # S % 4 != 0: scalar stratified kernel, partial rows in the scans
+    (1, 16, 16, 64, 36),     # S = 64 fast merge with the scalar plane transpose (HW % 128 != 0)
+])
+def test_render_vs_oracle_fallback_paths(nfi, B, H, W, S, res):
+    _check(*_oracle_vs_cuda(nfi, B, H, W, S, res, True, False, False, False, seed=3))
+
+
+def test_merge_fast_path_ties_and_unsorted_coarse(nfi):
+    """merge_composite's S = 64 fast path must hand rays with exactly equal fine depths, fine == coarse
+    ties and a non-ascending coarse list to the general path: permutation bit-exact against
+    torch.sort(stable=True) of cat(coarse, fine) (run.py:283-285) in every case."""
+    g = torch.Generator().manual_seed(5)
+    R, S = 64, 64
+    zc = torch.sort(torch.rand(R, S, generator=g) * 2 + 0.5, dim=-1).values
+    zf = torch.rand(R, S, generator=g) * 2 + 0.5
+    zf[1, 5] = zf[1, 40]                       # two equal fine depths
+    zf[2, 7] = zc[2, 20]                       # fine == coarse: coarse first
+    zc[3, 10], zc[3, 11] = zc[3, 11].clone(), zc[3, 10].clone()     # coarse not ascending
+    zf[4] = zf[4, 0]                           # all fine depths equal
+    zc[5] = zc[5, 0]; zf[5] = zc[5, 0]         # everything equal
+    coarse = torch.rand(R, S, 4, generator=g); fine = torch.rand(R, S, 4, generator=g)
+    d = torch.nn.functional.normalize(torch.randn(R, 3, generator=g), dim=-1)
+    rgb, depth, mask, perm, zs = nfi.ops.merge_composite(cu(coarse), cu(fine), cu(zc), cu(zf), cu(d), False)
+    ref = torch.sort(torch.cat((zc, zf), dim=-1), dim=-1, stable=True)
+    assert torch.equal(perm.cpu().long(), ref.indices)
+    assert torch.equal(zs.cpu(), ref.values)
