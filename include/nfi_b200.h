@@ -171,6 +171,20 @@ int nfi_merge_composite_bwd(const float* coarse, const float* fine, const float*
                             int white_background, const float* g_rgb_map, const float* g_mask,
                             float* g_coarse, float* g_fine, nfi_stream_t stream);
 
+/* ---- N3: F.normalize(q) + pose_utils.pose_to_matrix (run.py:2257-2262, lib/pose_utils.py:30-75) ----
+ * z0 [B] or NULL (orthographic), t2 [B,2], s [B], q [B,4] = (w, x, y, z) -> cam2world [B,16] and, for
+ * perspective poses, focal [B] = (1 + exp(z0)) / 2.  normalize_q != 0 folds q / max(|q|, 1e-12) in.
+ * Backward: g_cam2world [B,16], g_focal [B] or NULL -> g_z0 [B] (perspective; may be NULL), g_t2 [B,2],
+ * g_s [B], g_q [B,4] (all overwritten).  The orthographic branch divides per image (the evident intent
+ * of pose_utils.py:69, which the reference only gets right for B = 1). */
+int nfi_pose_to_matrix_fwd(const float* z0, const float* t2, const float* s, const float* q, int B,
+                           int camera_flipped, int normalize_q, float* cam2world, float* focal,
+                           nfi_stream_t stream);
+int nfi_pose_to_matrix_bwd(const float* z0, const float* t2, const float* s, const float* q, int B,
+                           int camera_flipped, int normalize_q, const float* g_cam2world,
+                           const float* g_focal, float* g_z0, float* g_t2, float* g_s, float* g_q,
+                           nfi_stream_t stream);
+
 /* ---- A11 / A12: the whole render (run.py:176-350) and its backward as ONE pair of calls ----------
  * Sequences A1-A10 above on `stream` inside a caller-owned workspace (nothing is allocated, nothing
  * synchronises).  Ray r = (b*H + h)*W + w.  planes_cl: see nfi_planes_to_cl.  focal NULL = orthographic,

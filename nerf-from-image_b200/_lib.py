@@ -40,6 +40,8 @@ class NfiRender(Structure):
 
 _P = c_void_p
 _SIGS = {
+    "nfi_pose_to_matrix_fwd": (c_int, [_P, _P, _P, _P, c_int, c_int, c_int, _P, _P, _P]),
+    "nfi_pose_to_matrix_bwd": (c_int, [_P, _P, _P, _P, c_int, c_int, c_int, _P, _P, _P, _P, _P, _P, _P]),
     "nfi_render_workspace_bytes": (ctypes.c_size_t, [POINTER(NfiRender), c_int]),
     "nfi_render_fwd": (c_int, [POINTER(NfiRender), _P, _P, _P, _P, _P]),
     "nfi_render_bwd": (c_int, [POINTER(NfiRender), _P, _P, _P, _P, _P, _P, _P, _P, c_int, _P]),

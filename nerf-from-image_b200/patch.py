@@ -5,6 +5,8 @@ Route (i), stage level -- `install_modules()`:
     sys.modules['lib.nerf_utils'] <- nfi_b200.nerf_utils            (lib/nerf_utils.py, 7 functions)
     models.generator.TriplanarDecoder.forward <- decoder.triplanar_decoder_forward
                                                                     (models/generator.py:301-331)
+    lib.pose_utils.pose_to_matrix <- nfi_b200.pose_utils.pose_to_matrix for CUDA tensors
+                                                                    (lib/pose_utils.py:48-75)
 Route (ii), fused -- `python -m nfi_b200.patch <script.py> [args...]` (or `run_script`): the script
 is compiled with its module-level `def render` (run.py:176-350; a plain global that
 ParallelModel.forward looks up at call time, run.py:597) replaced by `nfi_b200.render.make_render`
@@ -38,6 +40,23 @@ def install_modules(reference_root=None, patch_decoder=True):
     sys.modules["lib.nerf_utils"] = _nu
     setattr(lib_pkg, "nerf_utils", _nu)
     done.append("lib.nerf_utils")
+    # N3: lib.pose_utils keeps everything but pose_to_matrix (the rest is off the hot path)
+    try:
+        pu = importlib.import_module("lib.pose_utils")
+    except ImportError:
+        pu = None
+    if pu is not None and hasattr(pu, "pose_to_matrix"):
+        from . import pose_utils as _pu
+        if not hasattr(pu, "_nfi_reference_pose_to_matrix"):
+            pu._nfi_reference_pose_to_matrix = pu.pose_to_matrix
+
+            def pose_to_matrix(z0, t2, s, q, camera_flipped):
+                if not q.is_cuda:                      # CPU callers (dataset preparation) keep the original
+                    return pu._nfi_reference_pose_to_matrix(z0, t2, s, q, camera_flipped)
+                return _pu.pose_to_matrix(z0, t2, s, q, camera_flipped)
+
+            pu.pose_to_matrix = pose_to_matrix
+        done.append("lib.pose_utils.pose_to_matrix")
     if patch_decoder:
         try:
             gen = importlib.import_module("models.generator")

@@ -180,6 +180,33 @@ def golden_decoder():
         np.savez_compressed(os.path.join(OUT, "decoder_%s.npz" % name), **npy(out))
 
 
+def golden_pose():
+    """pose_utils.pose_to_matrix (lib/pose_utils.py:48-75) with F.normalize on the quaternion as the
+    inversion loop calls it (run.py:2257-2262), forward and gradients."""
+    pu = ref_loader.modules().pose_utils
+    g = torch.Generator().manual_seed(41)
+    B = 5
+    out = {}
+    for name, persp, flipped in (("persp_flip", True, True), ("persp", True, False), ("ortho_flip", False, True)):
+        B = 5 if persp else 1            # the reference's orthographic branch only works for one image
+        z0 = (torch.randn(B, generator=g) * 0.5).requires_grad_() if persp else None
+        t2 = (torch.randn(B, 2, generator=g) * 0.3).requires_grad_()
+        s = (torch.rand(B, generator=g) + 0.5).requires_grad_()
+        q = torch.randn(B, 4, generator=g).requires_grad_()
+        mat, focal = pu.pose_to_matrix(z0, t2, s, F.normalize(q, dim=-1), camera_flipped=flipped)
+        gm = torch.randn(B, 4, 4, generator=g)
+        gf = torch.randn(B, generator=g)
+        loss = (mat * gm).sum() + ((focal * gf).sum() if persp else 0)
+        leaves = ([z0] if persp else []) + [t2, s, q]
+        grads = torch.autograd.grad(loss, leaves)
+        d = dict(t2=t2, s=s, q=q, mat=mat, gm=gm, gf=gf)
+        if persp:
+            d.update(z0=z0, focal=focal, d_z0=grads[0])
+        d.update(d_t2=grads[-3], d_s=grads[-2], d_q=grads[-1])
+        out.update({"%s_%s" % (name, k): v for k, v in d.items()})
+    np.savez_compressed(os.path.join(OUT, "pose.npz"), **npy(out))
+
+
 def golden_render(only=()):
     """Whole `render` (run.py:176-350; eval_kitti_persp.py:43-230 for the z-buffer variant)."""
     cases = {
@@ -263,6 +290,9 @@ if __name__ == "__main__":
     if not only:
         golden_functions()
         golden_decoder()
-    golden_render(only)
+    if not only or "pose" in only:
+        golden_pose()
+    if only != ("pose",):
+        golden_render(only)
     for f in sorted(os.listdir(OUT)):
         print(f, os.path.getsize(os.path.join(OUT, f)))

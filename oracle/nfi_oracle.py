@@ -382,6 +382,40 @@ def zbuffer_depth(depth, d_unit, cam2world):
 
 
 # --------------------------------------------------------------------------------------
+# N3  pose parametrisation -> cam2world          lib/pose_utils.py:30-75
+# --------------------------------------------------------------------------------------
+def pose_matrix(z0, t2, s, q, camera_flipped: bool):
+    """(z0 [B] | None, t2 [B,2], s [B], unit quaternion q [B,4] = (w, x, y, z)) -> (cam2world [B,4,4],
+    focal [B] | None).  Row i of the rotation block is the rotated basis vector e_i
+    (pose_utils.py:30-46: v + 2 (w (u x v) + u x (u x v))); the translation column is R . t3 with
+    t3 = (t2 / s, f / s), f = 1 + exp(z0) (perspective) or (t2, 1) / s (orthographic); a flipped camera
+    negates columns 1..3 of the top three rows -- the translation included (pose_utils.py:60-62)."""
+    B = q.shape[0]
+    w, u = q[:, :1], q[:, 1:]
+    eye = torch.eye(3, dtype=q.dtype, device=q.device).unsqueeze(0).expand(B, -1, -1)
+    uu = u.unsqueeze(1).expand(-1, 3, -1)
+    uv = torch.cross(uu, eye, dim=2)
+    uuv = torch.cross(uu, uv, dim=2)
+    R = eye + 2 * (w.unsqueeze(1) * uv + uuv)
+    if z0 is not None:
+        f = 1 + z0.exp()
+        t3 = torch.cat((t2 / s.unsqueeze(-1), (f / s).unsqueeze(-1)), dim=-1)
+        focal = f / 2
+    else:
+        # the reference divides [B,3] by s [B] WITHOUT unsqueezing (pose_utils.py:69): it broadcasts over
+        # the last dimension and is only the intended per-image division for B = 1 (it raises for
+        # B not in {1, 3}); restated as written
+        t3 = torch.cat((t2, torch.ones_like(t2[:, :1])), dim=-1) / s
+        focal = None
+    trans = (t3[:, None, :] * R).sum(dim=-1)
+    top = torch.cat((R, trans.unsqueeze(-1)), dim=-1)                  # [B,3,4]
+    if camera_flipped:
+        top = torch.cat((top[..., :1], -top[..., 1:]), dim=-1)
+    bottom = torch.tensor([0.0, 0.0, 0.0, 1.0], dtype=q.dtype, device=q.device).expand(B, 1, 4)
+    return torch.cat((top, bottom), dim=1), focal
+
+
+# --------------------------------------------------------------------------------------
 # A11  the whole render                        run.py:176-350
 # --------------------------------------------------------------------------------------
 def render(planes, palette, fp: FieldParams, H: int, W: int, cam2world, focal=None, center=None,

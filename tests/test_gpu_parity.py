@@ -603,3 +603,35 @@ def test_merge_fast_path_ties_and_unsorted_coarse(nfi):
     ref = torch.sort(torch.cat((zc, zf), dim=-1), dim=-1, stable=True)
     assert torch.equal(perm.cpu().long(), ref.indices)
     assert torch.equal(zs.cpu(), ref.values)
+
+
+# ---------------------------------------------------------------- SURVEY.md 8(f) N3
+@pytest.mark.parametrize("name,persp,flipped", [("persp_flip", True, True), ("persp", True, False),
+                                                ("ortho_flip", False, True)])
+def test_pose_to_matrix_golden(nfi, name, persp, flipped):
+    """F.normalize(q) + pose_utils.pose_to_matrix (run.py:2257-2262) against the unmodified reference."""
+    from nfi_b200 import pose_utils
+    g = {k[len(name) + 1:]: v for k, v in load("pose").items() if k.startswith(name + "_")}
+    if name == "persp":
+        g = {k: v for k, v in g.items() if not k.startswith("flip_")}
+    z0 = cu(g["z0"]).requires_grad_() if persp else None
+    t2, s, q = [cu(g[k]).requires_grad_() for k in ("t2", "s", "q")]
+    mat, focal = pose_utils.pose_to_matrix(z0, t2, s, q, flipped, normalize_quaternion=True)
+    assert rel_err(mat.cpu(), g["mat"]) < 1e-6
+    loss = (mat * cu(g["gm"])).sum()
+    if persp:
+        assert rel_err(focal.cpu(), g["focal"]) < 1e-6
+        loss = loss + (focal * cu(g["gf"])).sum()
+    else:
+        assert focal is None
+    leaves = ([z0] if persp else []) + [t2, s, q]
+    keys = (["d_z0"] if persp else []) + ["d_t2", "d_s", "d_q"]
+    for a, k in zip(torch.autograd.grad(loss, leaves), keys):
+        assert rel_err(a.cpu(), g[k]) < 1e-5, k
+    # the plain signature (already-normalised quaternion) agrees with the fused one
+    qn = torch.nn.functional.normalize(q.detach(), dim=-1)
+    mat2, _ = pose_utils.pose_to_matrix(z0, t2, s, qn, flipped)
+    assert rel_err(mat2.cpu(), g["mat"]) < 1e-6
+    if not persp:
+        with pytest.raises(RuntimeError):
+            pose_utils.pose_to_matrix(None, t2.repeat(2, 1), s.repeat(2), q.repeat(2, 1), flipped)

@@ -56,7 +56,7 @@ def test_reference_scripts_have_one_swappable_render():
 @pytest.mark.reference
 @pytest.mark.skipif(not os.path.exists(REF), reason="reference checkout not present")
 def test_install_modules_swaps_nerf_utils_and_decoder():
-    saved = {k: sys.modules.get(k) for k in ("lib", "lib.nerf_utils", "models", "models.generator")}
+    saved = {k: sys.modules.get(k) for k in ("lib", "lib.nerf_utils", "lib.pose_utils", "models", "models.generator")}
     saved_path = list(sys.path)
     os.environ.setdefault("PYTHONDONTWRITEBYTECODE", "1")
     sys.dont_write_bytecode = True
@@ -72,6 +72,17 @@ def test_install_modules_swaps_nerf_utils_and_decoder():
             assert hasattr(gen.TriplanarDecoder, "_nfi_reference_forward")
             gen.TriplanarDecoder.forward = gen.TriplanarDecoder._nfi_reference_forward
             del gen.TriplanarDecoder._nfi_reference_forward
+        if "lib.pose_utils.pose_to_matrix" in done:
+            import torch
+            pu = sys.modules["lib.pose_utils"]
+            assert hasattr(pu, "_nfi_reference_pose_to_matrix")
+            # CPU tensors still go to the reference implementation (no CPU path in the library)
+            q = torch.nn.functional.normalize(torch.randn(2, 4), dim=-1)
+            mat, focal = pu.pose_to_matrix(torch.zeros(2), torch.zeros(2, 2), torch.ones(2), q, True)
+            ref = pu._nfi_reference_pose_to_matrix(torch.zeros(2), torch.zeros(2, 2), torch.ones(2), q, True)
+            assert torch.equal(mat, ref[0]) and torch.equal(focal, ref[1])
+            pu.pose_to_matrix = pu._nfi_reference_pose_to_matrix
+            del pu._nfi_reference_pose_to_matrix
     finally:
         sys.path[:] = saved_path
         for k, v in saved.items():
