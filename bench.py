@@ -238,6 +238,10 @@ def run_ours(args):
                      "launch_ms": bwd_ms, "launches_timed": len(bwd),
                      "share_of_step": (sum(bwd) / args.steps) / ms_step if ms_step else None,
                      "mlp_tflops_bwd_data": mlp_flops_bwd / (bwd_ms * 1e-3) / 1e12 if bwd_ms > 0 else None,
+                     # what ncu says actually limits this launch: not HBM, not the tensor pipe
+                     "measured_limiter": "SM->L2 reduction requests of the plane-gradient scatter "
+                                         "(l1tex__m_l1tex2xbar_req_cycles_active 68%, 27.6 GB of red.v4.f32 payload per "
+                                         "launch; profiles/r01e_field_ws_ncu_full_summary.txt), issue slots 50%",
                      "field_fwd_launch_ms": fwd_ms,
                      "field_fwd_share_of_step": (sum(fwd) / args.steps) / ms_step if ms_step else None},
     }
