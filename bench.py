@@ -239,9 +239,10 @@ def run_ours(args):
                      "share_of_step": (sum(bwd) / args.steps) / ms_step if ms_step else None,
                      "mlp_tflops_bwd_data": mlp_flops_bwd / (bwd_ms * 1e-3) / 1e12 if bwd_ms > 0 else None,
                      # what ncu says actually limits this launch: not HBM, not the tensor pipe
-                     "measured_limiter": "SM->L2 reduction requests of the plane-gradient scatter "
-                                         "(l1tex__m_l1tex2xbar_req_cycles_active 68%, 27.6 GB of red.v4.f32 payload per "
-                                         "launch; profiles/r01e_field_ws_ncu_full_summary.txt), issue slots 50%",
+                     "measured_limiter": "instruction streams of the gather / MLP-chain roles (5.8 ms with all memory traffic "
+                                         "removed) plus the SM->L2 request path shared by 27 GB of L1-missing texel reads and "
+                                         "27.6 GB of red.v4.f32 lines (l1tex__m_l1tex2xbar_req_cycles_active 68%; the scatter "
+                                         "runs at 68% of the measured L2 reduction cap) -- DESIGN.md 4.2",
                      "field_fwd_launch_ms": fwd_ms,
                      "field_fwd_share_of_step": (sum(fwd) / args.steps) / ms_step if ms_step else None},
     }
