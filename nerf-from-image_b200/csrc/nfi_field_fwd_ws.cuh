@@ -1,11 +1,11 @@
 // Warp-specialised, software-pipelined forward of the fused triplane field (one persistent CTA per
-// SM, 25 warps).  Roles talk through mbarriers only; no __syncthreads inside the tile loop.
+// SM, 13 warps).  Roles talk through mbarriers only; no __syncthreads inside the tile loop.
 //
-//   producers  (2 x 8 warps) phase 1 (coords -> texel offsets / weights) + phase 2 (gather) of tiles
+//   producers  (2 x 4 warps) phase 1 (coords -> texel offsets / weights) + phase 2 (gather) of tiles
 //                         i+1, i+2 (one per group) into a ring of UMMA A-operand tiles, while ...
 //   MMA thread (1 warp)   ... issues tcgen05.mma for whichever tile has its operands ready
 //                         (layer 0 of tile i+1 goes ahead of layer 1 of tile i), and ...
-//   epilogue   (8 warps)  ... runs softplus / hi-lo split / heads of tile i out of TMEM
+//   epilogue   (4 warps)  ... runs softplus / hi-lo split / heads of tile i out of TMEM
 //                         (two accumulator sets, so tile i+1's layer 0 never waits for tile i's heads).
 //
 // Barrier protocol per tile (ring indices advance only on tiles with at least one active sample):
@@ -30,8 +30,15 @@ namespace nfi_ftc {
 constexpr int kWsGroups = NFI_WS_GROUPS;          // producer groups: group g prepares tiles it % kWsGroups == g
 constexpr int kWsGroupWarps = NFI_WS_GROUP_WARPS; // warps per group
 constexpr int kWsRows = kTile / kWsGroupWarps;    // rows of the tile owned by one producer warp (16 or 32)
-constexpr int kWsProducerWarps = kWsGroups * kWsGroupWarps, kWsEpilogueWarps = 8;
-constexpr int kWsThreads = (kWsProducerWarps + kWsEpilogueWarps + 1) * 32;   // 800
+// 13 warps leave ptxas 126 registers per thread; with 8 epilogue warps (17 warps, 96 registers) the
+// gather cannot keep its 12 LDG.128 in flight and the launch is 13 % slower (2.82 vs 2.49 ms, config 2).
+#ifndef NFI_WS_EPI_WARPS
+#define NFI_WS_EPI_WARPS 4
+#endif
+constexpr int kWsProducerWarps = kWsGroups * kWsGroupWarps, kWsEpilogueWarps = NFI_WS_EPI_WARPS;   // 4 or 8
+static_assert(kWsEpilogueWarps == 4 || kWsEpilogueWarps == 8, "one or two epilogue warps per TMEM lane quarter");
+constexpr int kWsEpiQ = 4 / (kWsEpilogueWarps / 4);      // 16-column groups of the hidden layer per epilogue warp
+constexpr int kWsThreads = (kWsProducerWarps + kWsEpilogueWarps + 1) * 32;   // 416
 #ifndef NFI_WS_STAGES
 #define NFI_WS_STAGES 3
 #endif
@@ -303,7 +310,7 @@ field_fwd_ws_kernel(const Args a) {
           nfi_tc::mbar_wait(&sm.d0_full[c], cph);
           if (ew == 0 && lane == 0) NFI_TRACE(2, it, 0);
           nfi_tc::fence_after_sync();
-          nfi_mlp::epilogue0_at<2>(sm.w.b0, tmem + c * kAccCols + lane_off, (ew >> 2) * 32);
+          nfi_mlp::epilogue0_at<kWsEpiQ>(sm.w.b0, tmem + c * kAccCols + lane_off, (ew >> 2) * 32);
           nfi_tc::fence_before_sync();
           __syncwarp();
           if (lane == 0) nfi_tc::mbar_arrive(&sm.h_full[c]);
