@@ -170,7 +170,11 @@ def run_ours(args):
         grads = torch.autograd.grad(loss, [p, a, c, f])
         return (loss, rgb, depth, mask, *grads)
 
-    pipe = HostStepPipeline(chunk_step, B, n_chunks, dev)
+    if args.e2e_mode == "graph":
+        from nfi_b200.host_pipeline import GraphedHostStepPipeline
+        pipe = GraphedHostStepPipeline(chunk_step, B, n_chunks, dev, host_in, depth=args.e2e_depth)
+    else:
+        pipe = HostStepPipeline(chunk_step, B, n_chunks, dev)
 
     def e2e_step():
         pipe.run(host_in, host_out)                     # returns when the host results are complete
@@ -222,8 +226,9 @@ def run_ours(args):
                                "perspective, grads to planes/attention/cam/focal" % (B, H, W),
                    "rays_per_step_per_gpu": R, "l2": "inputs (planes %d MB + gradients) exceed the 126 MB L2; no flush"
                    % (B * PLANE_BYTES >> 20), "rng": "torch.rand uniforms drawn per step (parity mode)",
-                   "e2e": "pinned host buffers; %d chunks of %d images pipelined over copy-in / compute / copy-out streams"
-                   % (n_chunks, B // n_chunks)},
+                   "e2e": "pinned host buffers; %d chunks of %d images pipelined over copy-in / compute / copy-out streams%s"
+                   % (n_chunks, B // n_chunks,
+                      ", chunk step replayed as a CUDA graph" if args.e2e_mode == "graph" else "")},
         "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                 "steps": n_e2e, "ms_per_step": e2e_ms / n_e2e},
         "gpu_launches": launches,
@@ -378,6 +383,9 @@ def main():
     ap.add_argument("--res", type=int, default=128)
     ap.add_argument("--cpu-res", type=int, default=64, help="image size of the bounded CPU sample")
     ap.add_argument("--e2e-chunks", type=int, default=8, help="image chunks of the pipelined end-to-end leg")
+    ap.add_argument("--e2e-mode", choices=("graph", "eager"), default="graph",
+                    help="chunk step of the end-to-end leg: CUDA-graph replay or eager launches")
+    ap.add_argument("--e2e-depth", type=int, default=2, help="graph instances used round-robin (graph mode)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else max(args.warmup, 1)

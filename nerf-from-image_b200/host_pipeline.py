@@ -69,3 +69,76 @@ class HostStepPipeline:
         del keep
         from . import ops
         ops.raise_if_no_hits()          # deferred "no ray hits the box" checks of the chunks
+
+
+class GraphedHostStepPipeline(HostStepPipeline):
+    """Same three-stream pipeline with the chunk step captured as CUDA graphs (nfi_b200.graph).
+
+    A chunk of 1-2 images keeps the GPU busy for 1-3 ms, about as long as Python needs to launch its
+    ~100 kernels, so the eager pipeline is launch-bound.  Here `depth` GraphedStep instances of
+    `step_fn` are captured once on chunk-shaped buffers and used round-robin: the host->device copy
+    of chunk c lands directly in the input buffers of graph c % depth (free once chunk c - depth has
+    been replayed), the replay writes that graph's output buffers (free once chunk c - depth has
+    left for the host).  `step_fn` must be capturable (render with check_hits="defer").
+    """
+
+    def __init__(self, step_fn: Callable, batch: int, n_chunks: int, device: torch.device,
+                 example_host_in: Sequence[torch.Tensor], depth: int = 2):
+        super().__init__(step_fn, batch, n_chunks, device)
+        from .graph import GraphedStep
+        self.depth = max(1, min(depth, n_chunks))
+        example = [self._slice(t, 0).to(device) for t in example_host_in]
+        self.graphs = [GraphedStep(step_fn, example) for _ in range(self.depth)]
+        self.launches_per_chunk = self.graphs[0].launches_per_replay
+        pend = [t for g in self.graphs for t in g._pending]
+        self._hit_min = torch.ones((), dtype=pend[0].dtype, device=device) if pend else None
+
+    def run(self, host_in: Sequence[torch.Tensor], host_out: Sequence[torch.Tensor]):
+        comp = torch.cuda.current_stream(self.device)
+        n, d = self.n_chunks, self.depth
+        ev_in = [torch.cuda.Event() for _ in range(n)]
+        ev_done = [torch.cuda.Event() for _ in range(n)]
+        ev_out = [torch.cuda.Event() for _ in range(n)]
+        self.s_in.wait_stream(comp)
+        if self._hit_min is not None:
+            self._hit_min.fill_(1)
+
+        def copy_in(c):
+            g = self.graphs[c % d]
+            if c >= d:
+                self.s_in.wait_event(ev_done[c - d])
+            with torch.cuda.stream(self.s_in), torch.no_grad():
+                for dst, src in zip(g.inputs, host_in):
+                    dst.copy_(self._slice(src, c), non_blocking=True)
+                ev_in[c].record(self.s_in)
+
+        for c in range(min(d, n)):
+            copy_in(c)
+        scalars = [None] * len(host_out)
+        for c in range(n):
+            g = self.graphs[c % d]
+            comp.wait_event(ev_in[c])
+            if c >= d:
+                comp.wait_event(ev_out[c - d])
+            g.graph.replay()
+            for t in g._pending:                    # hit counters are rewritten by the next replay
+                torch.minimum(self._hit_min, t.min(), out=self._hit_min)
+            ev_done[c].record(comp)
+            if c + d < n:
+                copy_in(c + d)
+            self.s_out.wait_event(ev_done[c])
+            with torch.cuda.stream(self.s_out):
+                for k, (dst, src) in enumerate(zip(host_out, g.outputs)):
+                    src = src.detach()
+                    if dst.dim() == 0:
+                        scalars[k] = src.clone() if scalars[k] is None else scalars[k] + src
+                        if c == n - 1:
+                            dst.copy_(scalars[k], non_blocking=True)
+                    else:
+                        self._slice(dst, c).copy_(src, non_blocking=True)
+                ev_out[c].record(self.s_out)
+        self.s_out.synchronize()
+        comp.wait_stream(self.s_out)
+        if self._hit_min is not None and int(self._hit_min.item()) == 0:
+            from . import ops
+            raise RuntimeError(ops._NO_HIT_MSG)

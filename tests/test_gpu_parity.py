@@ -632,6 +632,45 @@ def test_graphed_step_matches_eager(nfi):
     assert gs.launches_per_replay == 16
 
 
+def test_graphed_host_pipeline_matches_eager_pipeline(nfi):
+    """host_pipeline.GraphedHostStepPipeline (chunk step replayed as CUDA graphs, two instances used
+    round-robin) against the eager HostStepPipeline on the same pinned host buffers; two runs, so the
+    buffers of both graph instances are reused."""
+    from nfi_b200 import host_pipeline
+    B, n_chunks = 4, 4
+    c = _crender_case(nfi, B=B, HW=32)
+    H, W, S = c["H"], c["W"], c["S"]
+
+    def step(planes, pal, cam, focal, target, u_s, u_p):
+        planes, pal, cam, focal = [t.requires_grad_() for t in (planes, pal, cam, focal)]
+        rgb, depth, mask = nfi.render.render_planes(planes, pal, c["fld"], H, W, cam, focal, None, None, S,
+                                                    randomize=True, u_strat=u_s, u_pdf=u_p, check_hits="defer")
+        loss = (rgb - target).abs().sum()
+        return (loss, rgb, depth, mask, *torch.autograd.grad(loss, [planes, pal, cam, focal]))
+
+    pin = lambda t: t.detach().cpu().contiguous().pin_memory()
+    host_in = [pin(t) for t in (c["planes"], c["pal"], c["cam"], c["focal"], c["target"], c["u_s"],
+                                c["u_p"].view(B, H * W, S))]
+    step_v = lambda p, a, cm, f, tg, us, up: step(p, a, cm, f, tg, us, up.reshape(-1, S))
+    shapes = ((), (B, H, W, 3), (B, H, W), (B, H, W), tuple(c["planes"].shape), tuple(c["pal"].shape), (B, 4, 4), (B,))
+    out_e = [torch.zeros(sh).pin_memory() for sh in shapes]
+    out_g = [torch.zeros(sh).pin_memory() for sh in shapes]
+    eager = host_pipeline.HostStepPipeline(step_v, B, n_chunks, torch.device("cuda", 0))
+    graphed = host_pipeline.GraphedHostStepPipeline(step_v, B, n_chunks, torch.device("cuda", 0), host_in, depth=2)
+    assert graphed.launches_per_chunk > 0
+    for trial in range(2):
+        if trial == 1:
+            host_in[0].mul_(1.01)
+            host_in[4].mul_(0.9)
+        eager.run(host_in, out_e)
+        graphed.run(host_in, out_g)
+        for k in range(4):
+            assert torch.equal(out_e[k], out_g[k]) if k else rel_err(out_g[0], out_e[0]) < 1e-6, k
+        for k in range(4, 8):
+            assert rel_err(out_g[k], out_e[k]) < 1e-5, k
+        assert float(out_g[2].abs().max()) > 0
+
+
 # ---------------------------------------------------------------- the paths the fast kernels fall back from
 @pytest.mark.parametrize("B,H,W,S,res", [
     (1, 10, 14, 32, 20),     # ragged image (linear tile order), row-major texels (res % 8 != 0), general merge
