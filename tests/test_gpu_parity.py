@@ -637,7 +637,7 @@ def test_graphed_host_pipeline_matches_eager_pipeline(nfi):
     round-robin) against the eager HostStepPipeline on the same pinned host buffers; two runs, so the
     buffers of both graph instances are reused."""
     from nfi_b200 import host_pipeline
-    B, n_chunks = 4, 4
+    B, n_chunks = 4, [1, 2, 1]                 # unequal chunks: two graph sizes
     c = _crender_case(nfi, B=B, HW=32)
     H, W, S = c["H"], c["W"], c["S"]
 
@@ -657,7 +657,7 @@ def test_graphed_host_pipeline_matches_eager_pipeline(nfi):
     out_g = [torch.zeros(sh).pin_memory() for sh in shapes]
     eager = host_pipeline.HostStepPipeline(step_v, B, n_chunks, torch.device("cuda", 0))
     graphed = host_pipeline.GraphedHostStepPipeline(step_v, B, n_chunks, torch.device("cuda", 0), host_in, depth=2)
-    assert graphed.launches_per_chunk > 0
+    assert sorted(graphed.launches_per_chunk) == [1, 2] and min(graphed.launches_per_chunk.values()) > 0
     for trial in range(2):
         if trial == 1:
             host_in[0].mul_(1.01)
