@@ -5,7 +5,9 @@ gradients -- is independent (run.py scatters along dim 0 through nn.DataParallel
 Rank r of G owns images [r*B/G, (r+1)*B/G); there is NO collective on the data path.  The helpers
 here are the host-side plumbing around that: shard bounds, slicing a batch of render arguments, and
 the one collective the inversion loop has -- gathering per-image report tensors at the end
-(run.py:2020-2027).  Works on any torch.distributed backend (NCCL on the GPUs, gloo in the CPU tests).
+(run.py:2020-2027) -- plus the gradient all-reduce of generator training for the parameters that live
+on this path (decoder weights, beta, alpha; the reference gets it implicitly from nn.DataParallel's
+gradient reduction, run.py:636-644).  Works on any torch.distributed backend (NCCL on the GPUs, gloo in the CPU tests).
 """
 from typing import Any, Dict, Optional, Sequence, Tuple
 
@@ -62,6 +64,30 @@ def gather_report(local: torch.Tensor, batch: int) -> torch.Tensor:
     dist.all_gather(parts, pad.contiguous())
     sizes = [shard_range(batch, r, world) for r in range(world)]
     return torch.cat([p[: b - a] for p, (a, b) in zip(parts, sizes)], dim=0)
+
+
+def allreduce_grads(grads: Sequence[Optional[torch.Tensor]], batch_weight: Optional[float] = None):
+    """Sum the gradients of parameters shared by all images (decoder W0/b0/W1/b1, beta, alpha) over the
+    ranks, in place, as ONE flat bucket (they are ~2.7 k floats in total: one collective of launch-latency
+    size, not one per tensor).  nn.DataParallel sums replica gradients (run.py:636-644), so the default is
+    a plain sum; `batch_weight` scales the result (e.g. 1 / world for a mean).  None entries are skipped."""
+    rank, world = rank_world()
+    live = [g for g in grads if g is not None]
+    if world == 1 or not live:
+        if batch_weight is not None:
+            for g in live:
+                g.mul_(batch_weight)
+        return grads
+    flat = torch.cat([g.reshape(-1).to(torch.float32) for g in live])
+    dist.all_reduce(flat, op=dist.ReduceOp.SUM)
+    if batch_weight is not None:
+        flat.mul_(batch_weight)
+    off = 0
+    for g in live:
+        n = g.numel()
+        g.copy_(flat[off:off + n].view_as(g))
+        off += n
+    return grads
 
 
 def max_over_ranks(value: float, device: Optional[torch.device] = None) -> float:

@@ -55,6 +55,14 @@ def _worker(rank, world, port, batch, q):
         t = nd.max_over_ranks(1.0 + rank)
         lo2, hi2, out = nd.render_sharded(lambda scale, x: x * scale, batch, {"x": full}, shared=(2.0,))
         ok = ok and (lo2, hi2) == (lo, hi) and (out is None if hi == lo else torch.equal(out, full[lo:hi] * 2))
+        # decoder-gradient bucket: every rank contributes (rank + 1) * pattern; None entries are skipped
+        pats = [torch.arange(6.).view(2, 3), None, torch.ones(4)]
+        grads = [None if p is None else p * (rank + 1) for p in pats]
+        nd.allreduce_grads(grads)
+        tot = sum(r + 1 for r in range(world))
+        ok = ok and grads[1] is None and torch.equal(grads[0], pats[0] * tot) and torch.equal(grads[2], pats[2] * tot)
+        nd.allreduce_grads(grads, batch_weight=1.0 / world)
+        ok = ok and torch.allclose(grads[0], pats[0] * tot)      # mean of equal contributions
         q.put((rank, bool(ok), t))
     finally:
         dist.destroy_process_group()
