@@ -111,9 +111,11 @@ def run_ours(args):
     fld = decoder.Field(*[fd[k].to(dev) for k in ("W0", "b0", "W1", "b1", "beta", "alpha")],
                         SCENE_RANGE, 10, True)
 
+    pdt = torch.bfloat16 if args.plane_dtype == "bf16" else torch.float32
+
     def step(planes, pal, cam, focal, target):
         rgb, depth, mask = render.render_planes(planes, pal, fld, H, W, cam, focal, None, None, S,
-                                                randomize=True, white_background=False)
+                                                randomize=True, white_background=False, plane_dtype=pdt)
         loss = (rgb - target).abs().mean() * B          # run.py:2236-2238 (l1)
         grads = torch.autograd.grad(loss, [planes, pal, cam, focal])
         return loss, rgb, depth, mask, grads
@@ -184,7 +186,7 @@ def run_ours(args):
     def chunk_step(p, a, c, f, tg):
         p, a, c, f = [t.requires_grad_() for t in (p, a, c, f)]
         rgb, depth, mask = render.render_planes(p, a, fld, H, W, c, f, None, None, S, randomize=True,
-                                                white_background=False, check_hits="defer")
+                                                white_background=False, check_hits="defer", plane_dtype=pdt)
         loss = (rgb - tg).abs().sum() * (1.0 / (H * W * 3))     # sums over chunks to .mean() * B
         grads = torch.autograd.grad(loss, [p, a, c, f])
         return (loss, rgb, depth, mask, *grads)
@@ -240,7 +242,7 @@ def run_ours(args):
     out = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak",
-        "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "vs_baseline": None, "dtype": "f32" if args.plane_dtype == "f32" else "f32 (bf16 plane reads)", "data": "synthetic",
         "config": {"workload": "config2: inversion render fwd+bwd, B=%d images/GPU, %dx%d rays, 64+64 samples/ray, "
                                "perspective, grads to planes/attention/cam/focal" % (B, H, W),
                    "rays_per_step_per_gpu": R, "l2": "inputs (planes %d MB + gradients) exceed the 126 MB L2; no flush"
@@ -406,6 +408,8 @@ def main():
     ap.add_argument("--e2e-mode", choices=("graph", "eager"), default="graph",
                     help="chunk step of the end-to-end leg: CUDA-graph replay or eager launches")
     ap.add_argument("--e2e-depth", type=int, default=2, help="graph instances used round-robin (graph mode)")
+    ap.add_argument("--plane-dtype", choices=("f32", "bf16"), default="f32",
+                    help="bf16: the gather reads a bfloat16 copy of the planes (the 1e-2 mode); default f32 (1e-4)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else max(args.warmup, 1)

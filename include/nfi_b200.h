@@ -54,6 +54,9 @@ typedef struct NfiField {
   int32_t attention_values; /* A; 0 -> wide-sigmoid RGB head (models/generator.py:665-666) */
   int32_t use_sdf;          /* 1: Laplace-CDF density (generator.py:629-636); 0: softplus(d-1) */
   float scene_range;        /* points are divided by this (generator.py:604); 1.0 for raw decoder coords */
+  int32_t planes_bf16;      /* bf16 mode (1e-2 contract): planes_cl points to a bfloat16 copy of the
+                             * channels-last planes (same texel order, 64 bytes per texel); plane gradients
+                             * stay fp32.  nfi_field_fwd / nfi_field_bwd without weight gradients only. */
 } NfiField;
 
 int nfi_version(void);

@@ -26,7 +26,8 @@ class NfiField(Structure):
     """Mirror of `struct NfiField` in include/nfi_b200.h."""
     _fields_ = [("W0", c_void_p), ("b0", c_void_p), ("W1", c_void_p), ("b1", c_void_p),
                 ("beta", c_void_p), ("alpha", c_void_p), ("n_out", c_int32),
-                ("attention_values", c_int32), ("use_sdf", c_int32), ("scene_range", c_float)]
+                ("attention_values", c_int32), ("use_sdf", c_int32), ("scene_range", c_float),
+                ("planes_bf16", c_int32)]
 
 
 class NfiRender(Structure):
@@ -166,7 +167,7 @@ def call(name, device_tensor, *args):
         raise NfiError("%s failed (%d): %s" % (name, rc, msg))
 
 
-def make_field_struct(W0, b0, W1, b1, beta, alpha, attention_values, use_sdf, scene_range):
+def make_field_struct(W0, b0, W1, b1, beta, alpha, attention_values, use_sdf, scene_range, planes_bf16=False):
     """Build an NfiField; the returned `keep` list must outlive the call (holds the tensors)."""
     keep = [f32c(W0), f32c(b0), f32c(W1), f32c(b1),
             f32c(beta) if use_sdf else None, f32c(alpha) if use_sdf else None]
@@ -174,5 +175,5 @@ def make_field_struct(W0, b0, W1, b1, beta, alpha, attention_values, use_sdf, sc
     assert keep[0].shape == (64, 32), "decoder.net[0].weight must be [64, 32] (models/generator.py:294-296)"
     assert keep[2].shape[1] == 64
     f = NfiField(ptr(keep[0]), ptr(keep[1]), ptr(keep[2]), ptr(keep[3]), ptr(keep[4]), ptr(keep[5]),
-                 n_out, int(attention_values), 1 if use_sdf else 0, float(scene_range))
+                 n_out, int(attention_values), 1 if use_sdf else 0, float(scene_range), 1 if planes_bf16 else 0)
     return f, keep

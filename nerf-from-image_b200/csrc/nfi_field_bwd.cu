@@ -376,16 +376,22 @@ extern "C" int nfi_field_bwd(const NfiField* field, const float* planes_cl, cons
   cudaStream_t st = nfi_cu(stream);
   const bool wp = g_points != nullptr;
   const bool want_w = want_weight_grads != 0 && g_params != nullptr;
+  NFI_REQUIRE(!(want_w && field->planes_bf16), NFI_ERR_UNSUPPORTED,
+              "nfi_field_bwd: decoder weight gradients are not available with a bf16 plane copy");
   if (!want_w) {
     const int grid = field_grid_chunks(a);
     const int smem = (int)sizeof(BwSmem);
-#define NFI_LAUNCH_BWS(P, M, W)                                                                         \
+#define NFI_LAUNCH_BWS1(P, M, W, H)                                                                     \
   do {                                                                                                  \
-    cudaError_t e = cudaFuncSetAttribute(field_bwd_ws_kernel<P, M, W>,                                  \
+    cudaError_t e = cudaFuncSetAttribute(field_bwd_ws_kernel<P, M, W, H>,                               \
                                          cudaFuncAttributeMaxDynamicSharedMemorySize, smem);            \
     NFI_REQUIRE(e == cudaSuccess, NFI_ERR_LAUNCH, "nfi_field_bwd: cudaFuncSetAttribute: %s",            \
                 cudaGetErrorString(e));                                                                 \
-    field_bwd_ws_kernel<P, M, W><<<grid, kBwThreads, smem, st>>>(a);                                    \
+    field_bwd_ws_kernel<P, M, W, H><<<grid, kBwThreads, smem, st>>>(a);                                 \
+  } while (0)
+#define NFI_LAUNCH_BWS(P, M, W)                                                                         \
+  do {                                                                                                  \
+    if (a.f.planes_bf16) NFI_LAUNCH_BWS1(P, M, W, true); else NFI_LAUNCH_BWS1(P, M, W, false);          \
   } while (0)
     if (points) {
       if (mode == 0) { if (wp) NFI_LAUNCH_BWS(true, 0, true); else NFI_LAUNCH_BWS(true, 0, false); }
@@ -395,6 +401,7 @@ extern "C" int nfi_field_bwd(const NfiField* field, const float* planes_cl, cons
       else           { if (wp) NFI_LAUNCH_BWS(false, 1, true); else NFI_LAUNCH_BWS(false, 1, false); }
     }
 #undef NFI_LAUNCH_BWS
+#undef NFI_LAUNCH_BWS1
     NFI_CHECK_LAUNCH("field_bwd_ws_kernel");
 #ifdef NFI_WS_TRACE
     if (const char* path = getenv("NFI_WS_TRACE_FILE")) {       // developer builds only: blocking dump

@@ -194,11 +194,12 @@ __device__ __forceinline__ bool bw_phase1(const Args& a, BwTable& tb, const BwIn
   return act;
 }
 
+template <bool BF16>
 __device__ __forceinline__ float4 bw_ldg(const char* base, uint32_t off) {
 #ifdef NFI_EXP_NOGATHER    // developer A/B: every sample reads texel 0 (L1 hits), timing only
   off = 0;
 #endif
-  return __ldg(reinterpret_cast<const float4*>(base + off));
+  return ldg_texel4<BF16>(base, off);
 }
 __device__ __forceinline__ void bw_fma4(float4& acc, const float4& v, float w) {
   acc.x = fmaf(v.x, w, acc.x); acc.y = fmaf(v.y, w, acc.y); acc.z = fmaf(v.z, w, acc.z); acc.w = fmaf(v.w, w, acc.w);
@@ -223,12 +224,13 @@ __device__ __forceinline__ float4 bw_weights(const float4& d) {
 // Texel order: 0 (x0,y0)  1 (x1,y0)  2 (x0,y1)  3 (x1,y1).
 //   dF/d ix = (v1 - v0) + ((v3 - v2) - (v1 - v0)) ty      dF/d iy = (v2 - v0) + ((v3 - v1) - (v2 - v0)) tx
 // (texel differences first: sums of the raw texels cancel to ~1e-4 relative in the pose gradient)
-template <bool WANT_PTS>
+template <bool WANT_PTS, bool BF16>
 __device__ __forceinline__ void bw_gather(const Args& a, const BwTable& tb, float* a_hi, float* a_lo, float* tq,
                                           int b, int w, int lane) {
   const int c4 = lane & 7;
   const float third = 1.f / 3.f;
-  const char* base = reinterpret_cast<const char*>(a.planes) + (int64_t)b * 3 * a.Hp * a.Wp * 128 + c4 * 16;
+  const char* base = reinterpret_cast<const char*>(a.planes) +
+                     (int64_t)b * 3 * a.Hp * a.Wp * (BF16 ? 64 : 128) + c4 * (BF16 ? 8 : 16);
 #pragma unroll 1
   for (int it = 0; it < kBwRows / 4; ++it) {
     const int li = it * 4 + (lane >> 3);
@@ -241,7 +243,8 @@ __device__ __forceinline__ void bw_gather(const Args& a, const BwTable& tb, floa
       for (int p = 0; p < 3; ++p) {
         const uint4 o = tb.toff[p][s];
         d[p] = tb.tder[p][s];
-        v[p][0] = bw_ldg(base, o.x); v[p][1] = bw_ldg(base, o.y); v[p][2] = bw_ldg(base, o.z); v[p][3] = bw_ldg(base, o.w);
+        v[p][0] = bw_ldg<BF16>(base, o.x); v[p][1] = bw_ldg<BF16>(base, o.y);
+        v[p][2] = bw_ldg<BF16>(base, o.z); v[p][3] = bw_ldg<BF16>(base, o.w);
       }
       float4 t[3];
 #pragma unroll
@@ -345,7 +348,7 @@ __device__ long long g_bw_trace[kBtRoles * kBtN * kBtEv];
 #define NFI_BTRACE(role, it, ev) do {} while (0)
 #endif
 
-template <bool PTS, int MODE, bool WANT_PTS>
+template <bool PTS, int MODE, bool WANT_PTS, bool BF16>
 __global__ void __launch_bounds__(kBwThreads, 1)
 field_bwd_ws_kernel(const Args a) {
   extern __shared__ __align__(128) unsigned char smem_raw[];
@@ -414,7 +417,7 @@ field_bwd_ws_kernel(const Args a) {
       if (bw_any(sm.meta[m])) {
         if (it >= 2) nfi_tc::mbar_wait(&sm.s_free[c], ((it >> 1) - 1) & 1);   // T / dF buffers c read
         if (w == 0 && lane == 0) NFI_BTRACE(0, it, 2);
-        bw_gather<WANT_PTS>(a, tb, sm.a[ca][0], sm.a[ca][1], sm.tq[q], b, w, lane);
+        bw_gather<WANT_PTS, BF16>(a, tb, sm.a[ca][0], sm.a[ca][1], sm.tq[q], b, w, lane);
         if (WANT_PTS) {
           nfi_tc::named_bar_sync(1 + q, 64);             // both halves of the quarter are in the scratch
           bw_store_t(sm.tq[q], tmem + lane_off + kBwColT + 96 * c, half, lane);

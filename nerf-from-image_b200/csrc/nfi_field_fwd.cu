@@ -124,15 +124,20 @@ extern "C" int nfi_field_fwd(const NfiField* field, const float* planes_cl, cons
   {
     const int grid = field_grid_chunks(a);
     const int smem = (int)sizeof(WsFwdSmem);
+#define NFI_LAUNCH_WS1(P, M, H)                                                           \
+  do {                                                                                    \
+    rc = set_smem(field_fwd_ws_kernel<P, M, H>, smem, "nfi_field_fwd");                   \
+    if (rc) return rc;                                                                    \
+    field_fwd_ws_kernel<P, M, H><<<grid, kWsThreads, smem, st>>>(a);                      \
+  } while (0)
 #define NFI_LAUNCH_WS(P, M)                                                               \
   do {                                                                                    \
-    rc = set_smem(field_fwd_ws_kernel<P, M>, smem, "nfi_field_fwd");                      \
-    if (rc) return rc;                                                                    \
-    field_fwd_ws_kernel<P, M><<<grid, kWsThreads, smem, st>>>(a);                         \
+    if (a.f.planes_bf16) NFI_LAUNCH_WS1(P, M, true); else NFI_LAUNCH_WS1(P, M, false);    \
   } while (0)
     if (points) { if (mode == 0) NFI_LAUNCH_WS(true, 0); else NFI_LAUNCH_WS(true, 1); }
     else        { if (mode == 0) NFI_LAUNCH_WS(false, 0); else NFI_LAUNCH_WS(false, 1); }
 #undef NFI_LAUNCH_WS
+#undef NFI_LAUNCH_WS1
     NFI_CHECK_LAUNCH("field_fwd_ws_kernel");
 #ifdef NFI_WS_TRACE
     if (const char* path = getenv("NFI_WS_TRACE_FILE")) {       // developer builds only: blocking dump

@@ -151,18 +151,17 @@ __device__ __forceinline__ bool ws_phase1(const Args& a, WsTables& tb, WsMeta& m
   return active;
 }
 
-__device__ __forceinline__ float4 ws_ldg(const char* base, uint32_t off) {
-  return __ldg(reinterpret_cast<const float4*>(base + off));
-}
 __device__ __forceinline__ void ws_fma4(float4& acc, const float4& v, float w) {
   acc.x = fmaf(v.x, w, acc.x); acc.y = fmaf(v.y, w, acc.y); acc.z = fmaf(v.z, w, acc.z); acc.w = fmaf(v.w, w, acc.w);
 }
 
 // phase 2 for the pipelined kernels: warp w of a group gathers rows 16w .. 16w+15, 8 lanes per texel
+template <bool BF16>
 __device__ __forceinline__ void ws_gather(const Args& a, const WsTables& tb, const WsMeta& mt, float* a_hi,
                                           float* a_lo, int b, int gw, int lane) {
   const int c4 = lane & 7;
-  const char* base = reinterpret_cast<const char*>(a.planes) + (int64_t)b * 3 * a.Hp * a.Wp * 128 + c4 * 16;
+  const char* base = reinterpret_cast<const char*>(a.planes) +
+                     (int64_t)b * 3 * a.Hp * a.Wp * (BF16 ? 64 : 128) + c4 * (BF16 ? 8 : 16);
 #pragma unroll 2
   for (int it = 0; it < kWsRows / 4; ++it) {
     const int s = gw * kWsRows + it * 4 + (lane >> 3);
@@ -174,7 +173,8 @@ __device__ __forceinline__ void ws_gather(const Args& a, const WsTables& tb, con
       for (int p = 0; p < 3; ++p) {
         const uint4 o = tb.toff[p][s];
         w[p] = tb.twgt[p][s];
-        v[p][0] = ws_ldg(base, o.x); v[p][1] = ws_ldg(base, o.y); v[p][2] = ws_ldg(base, o.z); v[p][3] = ws_ldg(base, o.w);
+        v[p][0] = ldg_texel4<BF16>(base, o.x); v[p][1] = ldg_texel4<BF16>(base, o.y);
+        v[p][2] = ldg_texel4<BF16>(base, o.z); v[p][3] = ldg_texel4<BF16>(base, o.w);
       }
 #pragma unroll
       for (int p = 0; p < 3; ++p) {
@@ -190,7 +190,7 @@ __device__ __forceinline__ void ws_gather(const Args& a, const WsTables& tb, con
 
 namespace nfi_ftc {
 
-template <bool PTS, int MODE>
+template <bool PTS, int MODE, bool BF16>
 __global__ void __launch_bounds__(kWsThreads, 1)
 field_fwd_ws_kernel(const Args a) {
   extern __shared__ __align__(128) unsigned char smem_raw[];
@@ -245,7 +245,7 @@ field_fwd_ws_kernel(const Args a) {
       if (gw == 0 && lane == 0 && g < 2) NFI_TRACE(g, it, 1);
       nfi_tc::mbar_wait(&sm.a_empty[s], ((it / kNS) & 1) ^ 1);
       if (gw == 0 && lane == 0 && g < 2) NFI_TRACE(g, it, 2);
-      if (wany) ws_gather(a, tab, mt, sm.a[s][0], sm.a[s][1], bcur, gw, lane);
+      if (wany) ws_gather<BF16>(a, tab, mt, sm.a[s][0], sm.a[s][1], bcur, gw, lane);
       nfi_tc::fence_proxy_async();
       __syncwarp();
       if (lane == 0) nfi_tc::mbar_arrive(&sm.a_full[s]);

@@ -44,6 +44,19 @@ struct Args {
   float* g_planes; float* g_palette; float* g_points; float* g_params;
 };
 
+// One 16-byte feature chunk (4 channels) of a texel.  `off` is the texel's byte offset in the fp32 layout
+// (128 bytes per texel); a bf16 plane copy (NfiField.planes_bf16, 64 bytes per texel, same texel order)
+// is read with half the offset and an 8-byte load, widened exactly (bf16 -> fp32 is a 16-bit shift).
+template <bool BF16>
+__device__ __forceinline__ float4 ldg_texel4(const char* base, uint32_t off) {
+  if (BF16) {
+    const uint2 r = __ldg(reinterpret_cast<const uint2*>(base + (off >> 1)));
+    return make_float4(__uint_as_float(r.x << 16), __uint_as_float(r.x & 0xFFFF0000u),
+                       __uint_as_float(r.y << 16), __uint_as_float(r.y & 0xFFFF0000u));
+  }
+  return __ldg(reinterpret_cast<const float4*>(base + off));
+}
+
 // (tile-in-image, thread) -> sample index WITHIN the image (ray_in_image * S + k), or -1.
 // 32-bit arithmetic: fill_args guarantees npi * S < 2^31.
 __device__ __forceinline__ int sample_in_image(const Args& a, int t, int tid) {

@@ -242,14 +242,20 @@ class _Field(Function):
 
     @staticmethod
     def forward(ctx, planes_cl, palette, W0, b0, W1, b1, beta, alpha, origins, dirs, z, points,
-                cfg, mode, img_w, skip_oob, want_probs, sink=None):
+                cfg, mode, img_w, skip_oob, want_probs, sink=None, planes_bf16=None):
         ctx.sink = sink
         pl = f32c(planes_cl)
+        # bf16 mode: the kernels gather from `planes_bf16` (a bfloat16 copy of planes_cl, same layout);
+        # planes_cl stays the autograd handle, so the plane gradient is fp32 like the master copy
+        if planes_bf16 is not None:
+            assert planes_bf16.dtype == torch.bfloat16 and planes_bf16.shape == pl.shape \
+                and planes_bf16.is_contiguous() and planes_bf16.device == pl.device
+        src = pl if planes_bf16 is None else planes_bf16
         B, _, Hp, Wp, C = pl.shape
         assert C == 32 and pl.shape[1] == 3
         pal = f32c(palette)
         field, keep = _lib.make_field_struct(W0, b0, W1, b1, beta, alpha, cfg.attention_values,
-                                             cfg.use_sdf, cfg.scene_range)
+                                             cfg.use_sdf, cfg.scene_range, planes_bf16 is not None)
         n_out = field.n_out
         if points is not None:
             pts = f32c(points)
@@ -268,9 +274,10 @@ class _Field(Function):
         probs = None
         if want_probs and mode == 0 and cfg.attention_values > 0:
             probs = _empty(pl, *lead, cfg.attention_values)
-        call("nfi_field_fwd", pl, field, ptr(pl), ptr(pal), B, Hp, Wp, ptr(o), ptr(d), ptr(zz), ptr(pts),
+        call("nfi_field_fwd", pl, field, ptr(src), ptr(pal), B, Hp, Wp, ptr(o), ptr(d), ptr(zz), ptr(pts),
              npi, S, mode, int(img_w), int(skip_oob), ptr(out), ptr(probs))
         ctx.save_for_backward(pl, pal, *keep[:4], keep[4], keep[5], o, d, zz, pts)
+        ctx.planes_bf16 = planes_bf16
         ctx.cfg, ctx.mode, ctx.img_w, ctx.npi, ctx.S = cfg, mode, int(img_w), npi, S
         ctx.oshape = None if origins is None else origins.shape
         ctx.pshape = None if points is None else points.shape
@@ -288,7 +295,8 @@ class _Field(Function):
         want_w = any(need[2:6])           # generator training (run.py:980-986)
         B, _, Hp, Wp, _ = pl.shape
         field, keep = _lib.make_field_struct(W0, b0, W1, b1, beta, alpha, cfg.attention_values,
-                                             cfg.use_sdf, cfg.scene_range)
+                                             cfg.use_sdf, cfg.scene_range, ctx.planes_bf16 is not None)
+        src = pl if ctx.planes_bf16 is None else ctx.planes_bf16
         n_out = field.n_out
         g = f32c(g_out)
         g_planes = ret_planes = None
@@ -303,7 +311,7 @@ class _Field(Function):
         want_params = want_w or (cfg.use_sdf and mode == 0 and (need[6] or need[7]))
         g_params = torch.zeros(sum(_param_sizes(n_out)), dtype=torch.float32, device=pl.device) \
             if want_params else None
-        call("nfi_field_bwd", pl, field, ptr(pl), ptr(pal), B, Hp, Wp, ptr(o), ptr(d), ptr(zz), ptr(pts),
+        call("nfi_field_bwd", pl, field, ptr(src), ptr(pal), B, Hp, Wp, ptr(o), ptr(d), ptr(zz), ptr(pts),
              ctx.npi, ctx.S, mode, ctx.img_w, ptr(g), ptr(g_planes), ptr(g_pal), ptr(g_points),
              ptr(g_params), int(want_w))
         go = gd = gp = None
@@ -329,7 +337,7 @@ class _Field(Function):
                 gW1 = g_params[o1:o2].view_as(W1) if need[4] else None
                 gb1 = g_params[o2:base].view_as(b1) if need[5] else None
         return (ret_planes, g_pal, gW0, gb0, gW1, gb1, g_beta, g_alpha, go, gd, None, gp,
-                None, None, None, None, None, None)
+                None, None, None, None, None, None, None)
 
 
 def decoder_mlp(feat, W0, b0, W1, b1, want_hidden=False):
@@ -344,19 +352,25 @@ def decoder_mlp(feat, W0, b0, W1, b1, want_hidden=False):
     return (y, hp) if want_hidden else y
 
 
+def planes_bf16_copy(planes_cl):
+    """bf16 mode: the bfloat16 copy of channels-last planes the kernels gather from (round to nearest
+    even, like Tensor.bfloat16()); pass it as `planes_bf16=` next to the fp32 planes_cl."""
+    return planes_cl.detach().to(torch.bfloat16).contiguous()
+
+
 def field_on_rays(planes_cl, palette, W0, b0, W1, b1, beta, alpha, origins, dirs, z, cfg,
-                  img_w=0, skip_oob=False, want_probs=False, sink=None):
+                  img_w=0, skip_oob=False, want_probs=False, sink=None, planes_bf16=None):
     """(sigma, r, g, b) [.., S, 4] for the samples o + d*z of every ray (no points tensor in HBM).
     `sink`: a PlaneGradSink shared with the other passes over the same planes_cl."""
     return _Field.apply(planes_cl, palette, W0, b0, W1, b1, beta, alpha, origins, dirs, z.detach(),
-                        None, cfg, 0, img_w, skip_oob, want_probs, sink)
+                        None, cfg, 0, img_w, skip_oob, want_probs, sink, planes_bf16)
 
 
 def field_on_points(planes_cl, palette, W0, b0, W1, b1, beta, alpha, points, cfg, mode=0,
-                    want_probs=False):
+                    want_probs=False, planes_bf16=None):
     """Heads (mode 0) or raw decoder output (mode 1) at explicit points [B, n, 3]."""
     return _Field.apply(planes_cl, palette, W0, b0, W1, b1, beta, alpha, None, None, None, points,
-                        cfg, mode, 0, False, want_probs)
+                        cfg, mode, 0, False, want_probs, None, planes_bf16)
 
 
 def _sdf_normals(planes_cl, W0, b0, W1, b1, cfg, origins, dirs, z, points, img_w):

@@ -24,7 +24,8 @@ def render_planes(planes, palette, field: Field, height: int, width: int, tform_
                   force_no_cam_grad: bool = False, zbuffer_depth: bool = False,
                   planes_layout: str = "nchw", u_strat=None, u_pdf=None, check_hits=True,
                   return_aux: bool = False, compute_normals: bool = False,
-                  compute_semantics: bool = False, compute_coords: bool = False):
+                  compute_semantics: bool = False, compute_coords: bool = False,
+                  plane_dtype: torch.dtype = torch.float32):
     """Render `B` images.  planes: [B,96,Hp,Wp] or [B,3,32,Hp,Wp] (layout 'nchw', the StyleGAN2
     output of models/generator.py:475-477) or [B,3,Hp,Wp,32] ('cl').  palette: attention values
     [B,A,3] (None for the plain RGB head).  Returns (rgb [B,H,W,3], depth [B,H,W], mask [B,H,W])
@@ -32,7 +33,10 @@ def render_planes(planes, palette, field: Field, height: int, width: int, tform_
     otherwise drawn with torch.rand in the reference's order (nerf_utils.py:115, :204).
     compute_normals / compute_semantics / compute_coords (run.py:186-188) add the
     forward-only maps aux["normals"] [B,H,W,3] and aux["semantics"] [B,H,W,A] (coords [B,H,W,3] take
-    the semantics slot, run.py:337-338); they imply `return_aux`."""
+    the semantics slot, run.py:337-338); they imply `return_aux`.
+    plane_dtype=torch.bfloat16 is the bf16 mode of the contract (1e-2 instead of 1e-4): the gather reads
+    a bfloat16 copy of the planes (half the texel bytes); everything after the load, and every gradient,
+    stays fp32.  Not available together with decoder weight gradients or the extra maps."""
     H, W, S = int(height), int(width), int(depth_samples_per_ray)
     cam = tform_cam2world
     B = cam.shape[0]
@@ -49,6 +53,11 @@ def render_planes(planes, palette, field: Field, height: int, width: int, tform_
         o_s, d_s = o, d
     planes_cl = planes if planes_layout == "cl" else ops.planes_to_channels_last(planes)
     wts = field.tensors()
+    assert plane_dtype in (torch.float32, torch.bfloat16), "plane_dtype: torch.float32 or torch.bfloat16"
+    pl16 = ops.planes_bf16_copy(planes_cl) if plane_dtype == torch.bfloat16 else None
+    if pl16 is not None:
+        assert not (compute_normals or compute_semantics or compute_coords), \
+            "bf16 mode covers rgb / depth / mask and their gradients"
     # A4-A6 on the coarse samples: (sigma, r, g, b) per sample
     extras = compute_normals or compute_semantics or compute_coords
     want_sem = compute_semantics and not compute_coords
@@ -56,7 +65,7 @@ def render_planes(planes, palette, field: Field, height: int, width: int, tform_
         assert field.cfg.attention_values > 0      # run.py:229
     sink = ops.PlaneGradSink() if fine_sampling else None     # coarse + fine: one gradient buffer
     coarse, probs_c = ops.field_on_rays(planes_cl, palette, *wts, o_s, d_s, z_c, field.cfg, img_w=W,
-                                        skip_oob=not want_sem, want_probs=want_sem, sink=sink)
+                                        skip_oob=not want_sem, want_probs=want_sem, sink=sink, planes_bf16=pl16)
     nrm_c = ops.sdf_normals_on_rays(planes_cl, *wts[:4], o_s, d_s, z_c, field.cfg, img_w=W) \
         if compute_normals else None
     aux = {"origins": o, "dirs": d, "near": near, "far": far, "z_coarse": z_c, "normals": None,
@@ -67,7 +76,7 @@ def render_planes(planes, palette, field: Field, height: int, width: int, tform_
             u_pdf = torch.rand((B * H * W, S), dtype=torch.float32, device=dev)
         z_f = ops.importance(coarse, d, z_c, u_pdf if randomize else None, sigma_stride=4)
         fine, probs_f = ops.field_on_rays(planes_cl, palette, *wts, o_s, d_s, z_f, field.cfg, img_w=W,
-                                          skip_oob=not want_sem, want_probs=want_sem, sink=sink)
+                                          skip_oob=not want_sem, want_probs=want_sem, sink=sink, planes_bf16=pl16)
         # A9 + A10
         rgb, depth, mask, perm, z_sorted = ops.merge_composite(
             coarse, fine, z_c, z_f, d, white_background, cam.detach() if zbuffer_depth else None)
