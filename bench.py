@@ -129,7 +129,7 @@ def run_ours(args):
     leaves = [t.to(dev).requires_grad_() for t in (planes_h, pal_h, cam_h, focal_h)]
     target = target_h.to(dev)
     torch.manual_seed(1234 + rank)
-    for _ in range(args.warmup):
+    for _ in range(1 if args.e2e_only else args.warmup):
         step(*leaves, target)
     barrier()
     sampler = ClockSampler(local)
@@ -141,7 +141,7 @@ def run_ours(args):
     barrier()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
-    for _ in range(args.steps):
+    for _ in range(1 if args.e2e_only else args.steps):
         step(*leaves, target)
     e1.record()
     barrier()
@@ -152,10 +152,15 @@ def run_ours(args):
     clocks = sampler.finish() if rank == 0 else None
 
     # ---- `e2e`: host buffers in, host buffers out, through the public API ---------------------
+    # the 1-GPU box has 4 GB of host memory: keep ONE host copy of the 403 MB planes (the pinned one)
     pin = lambda t: t.contiguous().pin_memory()
+    planes_shape, pal_shape = tuple(planes_h.shape), tuple(pal_h.shape)
     host_in = [pin(t) for t in (planes_h, pal_h, cam_h, focal_h, target_h)]
-    host_out = [pin(torch.empty(s)) for s in ((), (B, H, W, 3), (B, H, W), (B, H, W), tuple(planes_h.shape),
-                                              tuple(pal_h.shape), (B, 4, 4), (B,))]
+    del planes_h, pal_h, cam_h, focal_h, target_h
+    import gc
+    gc.collect()
+    host_out = [pin(torch.empty(s)) for s in ((), (B, H, W, 3), (B, H, W), (B, H, W), planes_shape,
+                                              pal_shape, (B, 4, 4), (B,))]
     h2d = sum(t.numel() * 4 for t in host_in)
     d2h = sum(t.numel() * 4 for t in host_out)
 
@@ -191,29 +196,63 @@ def run_ours(args):
         grads = torch.autograd.grad(loss, [p, a, c, f])
         return (loss, rgb, depth, mask, *grads)
 
-    if args.e2e_mode == "graph":
-        from nfi_b200.host_pipeline import GraphedHostStepPipeline
-        pipe = GraphedHostStepPipeline(chunk_step, B, n_chunks, dev, host_in, depth=args.e2e_depth)
-    else:
-        pipe = HostStepPipeline(chunk_step, B, n_chunks, dev)
-
-    def e2e_step():
-        pipe.run(host_in, host_out)                     # returns when the host results are complete
-        return float(host_out[0])
-
-    for _ in range(max(1, min(args.warmup, 3))):
-        e2e_step()
-    barrier()
     n_e2e = max(3, min(args.steps, 10))
-    t0 = time.perf_counter()
-    f0, f1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    f0.record()
-    for _ in range(n_e2e):
-        e2e_step()
-    f1.record()
-    barrier()
-    e2e_ms = f0.elapsed_time(f1)
-    del t0
+    e2e_note = None
+    try:
+        if args.e2e_mode == "graph":
+            from nfi_b200.host_pipeline import GraphedHostStepPipeline
+            pipe = GraphedHostStepPipeline(chunk_step, B, n_chunks, dev, host_in, depth=args.e2e_depth)
+        else:
+            pipe = HostStepPipeline(chunk_step, B, n_chunks, dev)
+        sizes = list(pipe.sizes)
+
+        def e2e_step():
+            pipe.run(host_in, host_out)                     # returns when the host results are complete
+            return float(host_out[0])
+
+        for _ in range(max(1, min(args.warmup, 3))):
+            e2e_step()
+        barrier()
+        if os.environ.get("NFI_BENCH_FAKE_E2E_FAULT") and not args.e2e_only:     # test hook for the path below
+            raise RuntimeError("injected end-to-end fault")
+        f0, f1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        f0.record()
+        for _ in range(n_e2e):
+            e2e_step()
+        f1.record()
+        barrier()
+        e2e_ms = f0.elapsed_time(f1)
+    except Exception as exc:           # noqa: BLE001 -- a CUDA fault here must not cost the whole bench line
+        if world > 1 or args.e2e_only:
+            raise
+        # One such fault was seen in ~1500 end-to-end runs this round.  The device-timed
+        # numbers above are already on the host; the CUDA context of this process is gone, so the
+        # end-to-end leg is measured once more in a fresh process.
+        sys.stderr.write("bench.py: end-to-end leg failed (%s); re-measuring it in a fresh process\n" % exc)
+        host_in = host_out = pipe = leaves = target = None        # give the host and device memory back first
+        gc.collect()
+        try:
+            torch.cuda.empty_cache()
+        except Exception:                                          # noqa: BLE001 -- the context may be gone
+            pass
+        import subprocess
+        # the fresh process uses the eager pipeline (argparse: the last --e2e-mode / --e2e-chunks win)
+        sub = subprocess.run([sys.executable, os.path.abspath(__file__)] + sys.argv[1:] +
+                             ["--e2e-only", "--e2e-mode", "eager", "--e2e-chunks", "8"],
+                             capture_output=True, text=True, timeout=900)
+        line = [l for l in sub.stdout.strip().splitlines() if l.startswith("{")]
+        if sub.returncode == 0 and line:
+            got = json.loads(line[-1])
+            e2e_ms, n_e2e, sizes = got["e2e_ms"], got["n_e2e"], got["sizes"]
+            args.e2e_mode = "eager"
+            e2e_note = "re-measured in a fresh process (eager chunk steps) after a CUDA fault in the first attempt"
+        else:
+            sys.stderr.write("bench.py: the fresh process failed too (rc %d):\n%s\n" % (sub.returncode, sub.stderr[-3000:]))
+            e2e_ms, sizes = None, []
+            e2e_note = "unmeasured: the end-to-end leg faulted twice (%s)" % str(exc)[:120]
+    if args.e2e_only:
+        print(json.dumps({"e2e_ms": e2e_ms, "n_e2e": n_e2e, "sizes": sizes}))
+        return
 
     # max over ranks
     if world > 1:
@@ -226,7 +265,7 @@ def run_ours(args):
         return
     ms_step = ms_total / args.steps
     value = world * R / (ms_step * 1e-3)
-    e2e_value = world * R / (e2e_ms / n_e2e * 1e-3)
+    e2e_value = world * R / (e2e_ms / n_e2e * 1e-3) if e2e_ms else None
     pk, pk_src = peaks()
     # dominant kernel: field_bwd_ws_kernel (one launch = one 64-sample pass over every ray)
     samples = R * S
@@ -248,10 +287,11 @@ def run_ours(args):
                    "rays_per_step_per_gpu": R, "l2": "inputs (planes %d MB + gradients) exceed the 126 MB L2; no flush"
                    % (B * PLANE_BYTES >> 20), "rng": "torch.rand uniforms drawn per step (parity mode)",
                    "e2e": "pinned host buffers; chunks of %s images pipelined over copy-in / compute / copy-out streams%s"
-                   % ("+".join(str(v) for v in pipe.sizes),
+                   % ("+".join(str(v) for v in sizes),
                       ", chunk step replayed as a CUDA graph" if args.e2e_mode == "graph" else "")},
         "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
-                "steps": n_e2e, "ms_per_step": e2e_ms / n_e2e},
+                "steps": n_e2e, "ms_per_step": (e2e_ms / n_e2e) if e2e_ms else None,
+                **({"note": e2e_note} if e2e_note else {})},
         "gpu_launches": launches,
         "clocks": clocks,
         "roofline": {"bound": "hbm", "kernel": "field_bwd_ws_kernel", "achieved": ach, "peak": pk["hbm_gbs"],
@@ -281,6 +321,9 @@ def run_ours(args):
     elif world > 1:
         out["cpu_baseline"] = None
     print(json.dumps(out))
+    if e2e_note:                  # the CUDA context of this process is broken: skip its destructors
+        sys.stdout.flush()
+        os._exit(0)
     if world > 1:
         dist.destroy_process_group()
 
@@ -411,6 +454,7 @@ def main():
     ap.add_argument("--plane-dtype", choices=("f32", "bf16"), default="f32",
                     help="bf16: the gather reads a bfloat16 copy of the planes (the 1e-2 mode); default f32 (1e-4)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--e2e-only", action="store_true", help=argparse.SUPPRESS)   # internal: see run_ours
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else max(args.warmup, 1)
     if args.impl == "reference":
