@@ -74,7 +74,7 @@ class ClockSampler(threading.Thread):
                 "reasons": reasons, "samples": len(sm)}
 
 
-NCU_BWD_DRAM_BYTES = 1165907000 + 576378624      # launch 10 of profiles/r01q_field_ws_ncu_full_summary.txt
+NCU_BWD_DRAM_BYTES = 1204762000 + 596777728      # launch 10 of profiles/r01z_field_ws_ncu_full_summary.txt
 
 
 def make_inputs(B, H, W, S, seed_shift=0):
@@ -297,9 +297,9 @@ def run_ours(args):
         "roofline": {"bound": "hbm", "kernel": "field_bwd_ws_kernel", "achieved": ach, "peak": pk["hbm_gbs"],
                      "unit": "GB/s", "frac": (ach / pk["hbm_gbs"]) if ach else None,
                      # dram__bytes_read.sum + dram__bytes_write.sum of one launch at this config, from the
-                     # committed ncu --set full capture (profiles/r01q_field_ws_ncu_full_summary.txt)
+                     # committed ncu --set full capture (profiles/r01z_field_ws_ncu_full_summary.txt)
                      "traffic": NCU_BWD_DRAM_BYTES if (B == 16 and H == 128) else None,
-                     "traffic_source": "profiles/r01q_field_ws_ncu_full_summary.txt",
+                     "traffic_source": "profiles/r01z_field_ws_ncu_full_summary.txt",
                      "peak_source": pk_src, "algorithmic_bytes_per_launch": a_bytes,
                      "launch_ms": bwd_ms, "launches_timed": len(bwd),
                      "share_of_step": (sum(bwd) / args.steps) / ms_step if ms_step else None,
