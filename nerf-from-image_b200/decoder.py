@@ -48,16 +48,25 @@ class Field:
 
 
 def _as_planes_tensor(xy, xz, yz):
-    """The three planes are views of one synthesis output (models/generator.py:475-477, 501-503);
-    recover it without a copy when possible."""
+    """The three planes are views `planes[:, k]` of one synthesis output viewed [B,3,32,Hp,Wp]
+    (models/generator.py:475-477, 501-503); recover that tensor as [B,96,Hp,Wp] without a copy when
+    they are.  The root of the view chain is whatever StyleGAN2 allocated -- for the real
+    SynthesisNetwork the grouped-conv / upsample buffer [B*96,1,Hp,Wp] (models/stylegan.py:72-76) --
+    so only its storage is trusted, never its shape."""
     base = xy._base
+    B, C, Hp, Wp = xy.shape
+    per_plane = C * Hp * Wp
+    dense = (3 * per_plane, Hp * Wp, Wp, 1)
+    esz = xy.element_size()
     if (base is not None and xz._base is base and yz._base is base and base.is_contiguous()
+            and base.numel() == 3 * xy.numel() and base.dtype == xy.dtype
+            and xy.shape == xz.shape == yz.shape
+            and xy.stride() == dense and xz.stride() == dense and yz.stride() == dense
             and xy.data_ptr() == base.data_ptr()
-            and base.numel() == 3 * xy.numel()
-            and xz.data_ptr() == base.data_ptr() + (xy.numel() // xy.shape[0]) * 4
-            and yz.data_ptr() == base.data_ptr() + 2 * (xy.numel() // xy.shape[0]) * 4):
-        return base
-    return torch.stack((xy, xz, yz), dim=1)
+            and xz.data_ptr() == base.data_ptr() + per_plane * esz
+            and yz.data_ptr() == base.data_ptr() + 2 * per_plane * esz):
+        return base.view(B, 3 * C, Hp, Wp)
+    return torch.stack((xy, xz, yz), dim=1).reshape(B, 3 * C, Hp, Wp)
 
 
 def triplanar_decoder_forward(self, xy, xz, yz, coords, requires_double_backward=False):

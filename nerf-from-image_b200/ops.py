@@ -7,6 +7,8 @@ once-differentiable.  Nothing here computes on the CPU or falls back to PyTorch 
 """
 from __future__ import annotations
 
+import threading
+
 import torch
 from torch.autograd import Function
 from torch.autograd.function import once_differentiable
@@ -70,7 +72,18 @@ def ray_bundle(H, W, focal, cam2world, bbox=None, center=None, normalize=False):
 # ---------------------------------------------------------------------------------------------
 _NO_HIT_MSG = ("compute_near_far_planes: no ray intersects the scene box "
                "(min(): expected a non-empty tensor)")
-_PENDING_HITS = []        # device hit counters of deferred checks (read back in one copy)
+
+
+class _Pending(threading.local):
+    """Device hit counters of deferred checks (read back in one copy).  Per host thread: the worker
+    threads of nn.DataParallel (run.py:636-644) each render on their own device and resolve their
+    own checks, so one thread never consumes -- or raises for -- another replica's counters."""
+
+    def __init__(self):
+        self.hits = []
+
+
+_PENDING = _Pending()
 
 
 def near_far(origins, dirs, scene_range, check_hits=True):
@@ -87,7 +100,7 @@ def near_far(origins, dirs, scene_range, check_hits=True):
     ws = _empty(o, NEARFAR_WS_BYTES, dtype=torch.uint8)
     call("nfi_near_far", o, ptr(o), ptr(d), R, float(scene_range), ptr(near), ptr(far), ptr(ws))
     if check_hits == "defer":
-        _PENDING_HITS.append(ws[:4].view(torch.int32))
+        _PENDING.hits.append(ws[:4].view(torch.int32))
     elif check_hits:
         hits = int(ws[:4].view(torch.int32).item())
         if hits == 0:
@@ -103,17 +116,17 @@ def count_launches():
 
 def take_pending_hits():
     """Hand the deferred hit counters to a caller that resolves them itself (nfi_b200.graph)."""
-    pending = list(_PENDING_HITS)
-    del _PENDING_HITS[:]
+    pending = list(_PENDING.hits)
+    del _PENDING.hits[:]
     return pending
 
 
 def raise_if_no_hits():
     """Resolve the deferred checks of near_far(check_hits="defer")."""
-    if not _PENDING_HITS:
+    if not _PENDING.hits:
         return
-    pending = list(_PENDING_HITS)
-    del _PENDING_HITS[:]
+    pending = list(_PENDING.hits)
+    del _PENDING.hits[:]
     by_dev = {}
     for t in pending:
         by_dev.setdefault(t.device, []).append(t)

@@ -118,7 +118,16 @@ def render_planes(planes, palette, field: Field, height: int, width: int, tform_
 
 
 def _closure_vars(fn):
-    return dict(zip(fn.__code__.co_freevars, (c.cell_contents for c in fn.__closure__ or ())))
+    """Free variables of the reference's `sampler` closure (models/generator.py:587).  Cells that the
+    generator never assigned stay out of the result: `viewdir_mapper_closure` only exists with
+    use_viewdir (generator.py:468-469), `attention_values` only with attention_values > 0 (:451-463)."""
+    out = {}
+    for name, cell in zip(fn.__code__.co_freevars, fn.__closure__ or ()):
+        try:
+            out[name] = cell.cell_contents
+        except ValueError:          # empty cell
+            pass
+    return out
 
 
 def make_render(args, dataset_config, zbuffer_depth: bool = False):

@@ -4,7 +4,9 @@ Nothing in the product package may import this module.  It exists so that
 `oracle/make_golden.py` and `tests/test_oracle_vs_reference.py` can run the
 reference's own code (in the build container, where /root/reference is mounted)
 and pin `oracle/nfi_oracle.py` + the golden fixtures under tests/golden/ to it.
-On the GPU box /root/reference does not exist and `available()` returns False.
+On the GPU box /root/reference does not exist; the loader then uses the unmodified files staged in
+git-ignored `oracle/_ref/` by `oracle/build_ref.py` (they travel with the snapshot), and
+`available()` is False only when neither exists.
 
 `run.py` cannot be imported (argparse + missing deps at module level,
 run.py:42), so `render` (run.py:176-350) and the z-buffer variant
@@ -16,7 +18,20 @@ import os
 import sys
 import types
 
-REF_ROOT = os.environ.get("NFI_REFERENCE", "/root/reference")
+_STAGED = os.path.join(os.path.dirname(os.path.abspath(__file__)), "_ref")
+
+
+def _pick_root():
+    """The mounted checkout where it exists (build container), else the copy staged by
+    oracle/build_ref.py into git-ignored oracle/_ref/ (this is what the GPU box sees)."""
+    cands = [os.environ.get("NFI_REFERENCE"), "/root/reference", _STAGED]
+    for c in cands:
+        if c and os.path.isfile(os.path.join(c, "lib", "nerf_utils.py")):
+            return c
+    return "/root/reference"
+
+
+REF_ROOT = _pick_root()
 
 
 def available() -> bool:
@@ -46,8 +61,11 @@ def modules():
 
 
 def lift_render(script="run.py", *, use_viewdir=False, use_sdf=True, attention_values=10,
-                fine_sampling=True, scene_range=1.4, white_background=False):
-    """Return the reference's `render` function bound to the given args/dataset_config globals."""
+                fine_sampling=True, scene_range=1.4, white_background=False, nerf_utils=None):
+    """Return the reference's `render` function bound to the given args/dataset_config globals.
+    `nerf_utils`: the module the lifted function sees under that name (default: the reference's own
+    lib.nerf_utils; the drop-in tests pass the replacement module, as `import lib.nerf_utils` would
+    resolve after `nfi_b200.patch.install_modules()`)."""
     import torch
     import torch.nn.functional as F
     m = modules()
@@ -57,7 +75,7 @@ def lift_render(script="run.py", *, use_viewdir=False, use_sdf=True, attention_v
     assert len(fn) == 1
     mod = ast.Module(body=fn, type_ignores=[])
     ns = {
-        "torch": torch, "F": F, "nerf_utils": m.nerf_utils, "pose_utils": m.pose_utils,
+        "torch": torch, "F": F, "nerf_utils": nerf_utils or m.nerf_utils, "pose_utils": m.pose_utils,
         "args": types.SimpleNamespace(use_viewdir=use_viewdir, use_sdf=use_sdf,
                                       attention_values=attention_values,
                                       fine_sampling=fine_sampling),
