@@ -445,3 +445,19 @@ extern "C" int nfi_field_bwd(const NfiField* field, const float* planes_cl, cons
   NFI_CHECK_LAUNCH("field_bwd_tc_kernel");
   return NFI_OK;
 }
+
+#ifdef NFI_WAIT_FLAG
+// Developer reproducer builds only (not declared in include/nfi_b200.h, absent from the shipped library):
+// number of bounded mbarrier waits of this translation unit that ran out of spins since the last reset.
+// Synchronises the device.
+extern "C" int nfi_debug_wait_timeouts(int reset) {
+  int v = -1;
+  if (cudaDeviceSynchronize() != cudaSuccess) return -2;
+  if (cudaMemcpyFromSymbol(&v, nfi_tc::g_nfi_wait_timeouts, sizeof(int)) != cudaSuccess) return -3;
+  if (reset) {
+    const int zero = 0;
+    if (cudaMemcpyToSymbol(nfi_tc::g_nfi_wait_timeouts, &zero, sizeof(int)) != cudaSuccess) return -4;
+  }
+  return v;
+}
+#endif

@@ -30,6 +30,26 @@
 //   acc_ready     epilogue -> MMA                    next A operand (H, dY, dHpre) is in TMEM
 //   df_full[c]    MMA (commit) -> scatter            dF buffer c is complete
 //   s_free[c]     scatter -> gather                  T and dF buffers c have been read (every tile)
+//
+// Phase discipline (audited in round 2 after the round-1 launch failure).  A parity wait is sound only
+// while the waiter is at most one phase behind the barrier, so for every barrier the arrival that
+// completes phase k + 1 must be ordered after every waiter's test of phase k:
+//   barrier       arrives (per tile)   waits                     why phase k + 1 cannot complete before the test of k
+//   meta_full[m]  gather, every tile   all roles, every tile     meta_full(it + 8) needs meta_empty(it + 5): every role past it
+//   meta_empty[m] E + S + MMA, every   gather, every tile >= 3   phase of tile r + 8 needs the gather's own meta_full(r + 8)
+//   a_full[c]     gather, every tile   MMA and scatter, EVERY    gather(it + 2) first waits a_empty(it) [MMA past its test]
+//                                      tile                      and s_free(it) [all scatter warps past their test]
+//   a_empty[c]    MMA, every tile      gather, every tile        a_empty(it) needs a_full(it), posted after the gather's test
+//   s_free[c]     scatter, every tile  gather, EVERY tile >= 2   scatter(it) arrives after a_full(it), posted after the test
+//   df_full[c]    MMA, active tiles    scatter, active tiles     self-counted; dF(it + 2k) needs a_full <- s_free(it) or meta_empty
+//   acc_full / acc_ready               strict ping-pong MMA <-> epilogue, self-counted phases
+// Round 1 waited for a_full[c] (scatter) and s_free[c] (gather) on ACTIVE tiles only.  A gather running
+// through an idle tile it + 2 then skipped s_free(it) and could complete phase (it >> 1) + 1 of a_full[c]
+// before a delayed scatter warp had tested phase it >> 1 for the active tile it; that warp then waited for a
+// parity only tile it + 4 could produce, and tile it + 4 needs meta_empty(it + 1) from the same warp:
+// deadlock -> bounded wait -> trap ("unspecified launch failure" after ~50 s).  Making only
+// the gather's wait unconditional would open the mirror-image race (scatter arriving on s_free for an
+// idle tile before a slow gather warp has tested the previous phase), so BOTH waits are unconditional.
 #pragma once
 #include "nfi_field_tc.cuh"
 
@@ -414,8 +434,13 @@ field_bwd_ws_kernel(const Args a) {
       // completes one phase of the barrier, so the parity test is only sound one phase behind
       const uint32_t ca = kBwNA == 2 ? c : 0u;
       nfi_tc::mbar_wait(&sm.a_empty[ca], (((kBwNA == 2 ? it >> 1 : it)) & 1) ^ 1);
+      // T / dF buffers c read by the scatter warps (tile it - 2).  Waited for on idle tiles too, like
+      // a_empty -- see "Phase discipline" at the top of the file
+#ifdef NFI_BW_OLD_PROTOCOL    // developer reproducer of the round-1 protocol (tests/test_ws_protocol.py)
+      if (bw_any(sm.meta[m]))
+#endif
+      if (it >= 2) nfi_tc::mbar_wait(&sm.s_free[c], ((it >> 1) - 1) & 1);
       if (bw_any(sm.meta[m])) {
-        if (it >= 2) nfi_tc::mbar_wait(&sm.s_free[c], ((it >> 1) - 1) & 1);   // T / dF buffers c read
         if (w == 0 && lane == 0) NFI_BTRACE(0, it, 2);
         bw_gather<WANT_PTS, BF16>(a, tb, sm.a[ca][0], sm.a[ca][1], sm.tq[q], b, w, lane);
         if (WANT_PTS) {
@@ -571,8 +596,14 @@ field_bwd_ws_kernel(const Args a) {
       const bool any = bw_any(sm.meta[m]) != 0;
       float gp[3] = {0.f, 0.f, 0.f};
       float g0[16], g1[16];
+#ifdef NFI_BW_INJECT_SCATTER_DELAY   // developer reproducer: one scatter warp falls behind now and then
+      if (sw == 3 && (it % 5u) == 1u) for (int d = 0; d < NFI_BW_INJECT_SCATTER_DELAY; ++d) __nanosleep(1000);
+#endif
+#ifdef NFI_BW_OLD_PROTOCOL
+      if (any)
+#endif
+      nfi_tc::mbar_wait(&sm.a_full[c], (it >> 1) & 1);            // T buffer c written; every tile (phase discipline)
       if (any) {
-        nfi_tc::mbar_wait(&sm.a_full[c], (it >> 1) & 1);          // T buffer c written (long ago)
         nfi_tc::mbar_wait(&sm.df_full[c], dfph[c]); dfph[c] ^= 1;
         if (sw == 0 && lane == 0) NFI_BTRACE(1, it, 0);
         nfi_tc::fence_after_sync();

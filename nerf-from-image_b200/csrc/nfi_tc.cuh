@@ -102,15 +102,33 @@ __device__ __forceinline__ uint32_t mbar_test(uint64_t* bar, uint32_t parity) {
   return ok;
 }
 // Bounded wait: a protocol bug must surface as a launch error (trap), never as a hung GPU.
+#ifndef NFI_WAIT_SPINS
+#define NFI_WAIT_SPINS (1u << 24)      // ~50 s of polling; developer reproducers lower it
+#endif
+#ifdef NFI_WAIT_FLAG
+// Developer reproducer builds only (tests/test_ws_protocol.py): a wait that runs out of spins raises a
+// device flag instead of trapping (a trap is an Xid on a shared box); once the flag is up every wait
+// falls through, so the launch drains quickly with meaningless results and the host reads the flag.
+__device__ int g_nfi_wait_timeouts;
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+  uint32_t spins = 0;
+  while (!mbar_try_wait(bar, parity)) {
+    ++spins;
+    if ((spins & 255u) == 0 && *(volatile int*)&g_nfi_wait_timeouts != 0) return;
+    if (spins > NFI_WAIT_SPINS) { atomicAdd(&g_nfi_wait_timeouts, 1); return; }
+  }
+}
+#else
 __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
   uint32_t spins = 0;
   while (!mbar_try_wait(bar, parity)) {
 #ifdef NFI_WAIT_SLEEP
     __nanosleep(NFI_WAIT_SLEEP);
 #endif
-    if (++spins > (1u << 24)) __trap();
+    if (++spins > NFI_WAIT_SPINS) __trap();
   }
 }
+#endif
 // thread arrival (release.cta): the arriving thread's earlier shared-memory writes are visible to
 // a thread that observes the phase completion
 __device__ __forceinline__ void mbar_arrive(uint64_t* bar) {

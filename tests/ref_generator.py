@@ -12,9 +12,9 @@ import ref_loader
 
 
 def build_generator(device="cpu", attention_values=10, use_sdf=True, scene_range=1.4, seed=0,
-                    sdf_shift=-0.6):
+                    sdf_shift=-1.0):
     """Random-init p3d_car-style generator (run.py:560-574 `create_model`).  The SDF bias is shifted so
-    that the rendered mask is non-trivial at random init (mean SDF ~ +0.65 otherwise: empty scene)."""
+    that the rendered mask is non-trivial at random init (mean SDF ~ +0.65 otherwise: empty scene; -1.0 gives a mask mean of ~0.37)."""
     m = ref_loader.modules()
     torch.manual_seed(seed)
     G = m.generator.Generator(512, scene_range, attention_values=attention_values, use_viewdir=False,

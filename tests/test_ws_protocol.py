@@ -1,0 +1,96 @@
+"""Reproducer for the round-1 `unspecified launch failure` of the warp-specialised field backward
+(csrc/nfi_field_bwd_ws.cuh, "Phase discipline").
+
+Cause: the scatter warps waited for a_full[c] and the gather warps for s_free[c] on ACTIVE tiles only; a
+gather that ran through an idle tile could complete a_full[c] one phase further than a delayed scatter warp
+was about to test, the parity wait aliased, the pipeline deadlocked and the bounded wait trapped after
+~50 s.  The trigger needs (a) active and idle tiles alternating with period 4 along a CTA's tile sequence and
+(b) one scatter warp held up between two tiles -- rare on an idle box (a second CUDA context time-slicing
+the GPU was alive at all three sightings), certain with an injected delay.
+
+Three builds of the library are used (lib/libnfi_b200_<name>.so, built by __graft_entry__.build() /
+`python tools/build_protocol_variants.py`; they carry -DNFI_WAIT_FLAG so that a wait which runs out of
+spins raises a device flag and the launch drains instead of trapping -- no Xid on a shared box):
+  shipped                      the product library, alternating active / idle tiles, many launches
+  newproto_delay               shipped protocol + injected scatter delay            -> 0 timed-out waits
+  oldproto_delay               round-1 protocol (-DNFI_BW_OLD_PROTOCOL) + the delay -> timed-out waits
+"""
+import os
+import subprocess
+import sys
+
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+LIBDIR = os.path.join(ROOT, "nerf-from-image_b200", "lib")
+
+_DRIVER = r'''
+import ctypes, os, sys, torch
+sys.path.insert(0, %(root)r)
+from nfi_b200 import _lib, ops, decoder, synth
+lib = _lib.lib()
+dbg = getattr(lib, "nfi_debug_wait_timeouts", None)
+if dbg is not None:
+    dbg.restype = ctypes.c_int; dbg.argtypes = [ctypes.c_int]
+B, H, W, S, res = 2, 64, 64, 64, 64
+dev = "cuda"
+planes = synth.make_planes(B, res=res, seed=1).to(dev)
+fd = synth.make_field(planes.cpu(), seed=3)
+fld = decoder.Field(*[fd[k].to(dev) for k in ("W0", "b0", "W1", "b1", "beta", "alpha")], 1.4, 10, True)
+pal = synth.make_palette(B, 10, seed=4).to(dev)
+cam, focal = synth.make_cameras(B, seed=2, perspective=True)
+o, d = ops.ray_bundle(H, W, focal.to(dev), cam.to(dev), None, None, normalize=True)
+near, far = ops.near_far(o, d, 1.4)
+z = ops.stratified(near, far, S, False, None)
+pcl = ops.planes_to_channels_last(planes).detach().requires_grad_()
+o = o.detach().requires_grad_(); d = d.detach().requires_grad_()
+# upstream gradient: depth steps k with k %% 4 in {0, 1} carry gradient, the others are exactly zero ->
+# along a CTA's tile sequence (consecutive depth steps of one pixel block) tiles go active, active, idle, idle
+k = torch.arange(S, device=dev)
+on = ((k %% 4) < 2).float().view(S, 1)                       # broadcast over [..., S, 4]
+worst = 0
+ref = None
+for rep in range(%(reps)d):
+    out, _ = ops.field_on_rays(pcl, pal, *fld.tensors(), o, d, z, fld.cfg, img_w=W, skip_oob=True)
+    up = torch.randn(out.shape, device=dev, generator=torch.Generator(device=dev).manual_seed(7)) * on
+    gp, go, gd = torch.autograd.grad(out, [pcl, o, d], up)
+    if dbg is not None:
+        worst = max(worst, dbg(1))
+    else:
+        torch.cuda.synchronize()
+    if ref is None:
+        ref = (gp.clone(), go.clone(), gd.clone())
+    elif dbg is None or worst == 0:
+        for a, b in zip((gp, go, gd), ref):
+            err = float((a - b).abs().max() / b.abs().max().clamp_min(1e-30))
+            assert err < 1e-4, err
+print("TIMEOUTS", worst)
+'''
+
+
+def _run(libname, reps):
+    env = dict(os.environ)
+    if libname:
+        path = os.path.join(LIBDIR, "libnfi_b200_%s.so" % libname)
+        if not os.path.exists(path):
+            pytest.skip("%s not built (python tools/build_protocol_variants.py)" % path)
+        env["NFI_B200_LIB"] = path
+    r = subprocess.run([sys.executable, "-c", _DRIVER % {"root": ROOT, "reps": reps}], env=env,
+                       capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-4000:]
+    return int(r.stdout.strip().splitlines()[-1].split()[1])
+
+
+def test_alternating_active_and_idle_tiles_shipped_library():
+    assert _run(None, reps=50) == 0
+
+
+def test_injected_scatter_delay_is_harmless_with_the_shipped_protocol():
+    assert _run("newproto_delay", reps=3) == 0
+
+
+def test_injected_scatter_delay_deadlocks_the_round1_protocol():
+    """The round-1 wait discipline, same delay: waits run out of spins (the launch failure of round 1)."""
+    assert _run("oldproto_delay", reps=3) > 0

@@ -1,0 +1,39 @@
+"""Build the two developer variants of libnfi_b200.so that tests/test_ws_protocol.py uses to reproduce the
+round-1 pipeline deadlock of the field backward (see that file).  Output: nerf-from-image_b200/lib/
+libnfi_b200_{newproto_delay,oldproto_delay}.so (git-ignored, travel to the GPU box with the snapshot)."""
+import os
+import subprocess
+import sys
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, os.path.join(HERE, "..", "nerf-from-image_b200"))
+import build as B  # noqa: E402
+
+COMMON = ["-DNFI_WAIT_FLAG", "-DNFI_WAIT_SPINS=(1u<<18)", "-DNFI_BW_INJECT_SCATTER_DELAY=60"]
+VARIANTS = {"newproto_delay": COMMON, "oldproto_delay": COMMON + ["-DNFI_BW_OLD_PROTOCOL"]}
+SRC = "nfi_field_bwd.cu"
+
+
+def build(force=False):
+    B.build()
+    src = os.path.join(B.CSRC, SRC)
+    deps = [src] + [os.path.join(B.CSRC, f) for f in os.listdir(B.CSRC) if f.endswith(".cuh")]
+    procs = []
+    for name, flags in VARIANTS.items():
+        lib = os.path.join(B.LIBDIR, "libnfi_b200_%s.so" % name)
+        if not force and not B._stale(lib, deps + [os.path.abspath(__file__)]):
+            continue
+        o = os.path.join(B.LIBDIR, "proto_%s.o" % name)
+        cmd = [B._nvcc()] + B.NVCC_FLAGS + flags + ["-c", src, "-o", o]
+        procs.append((name, o, lib, subprocess.Popen(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT)))
+    for name, o, lib, p in procs:
+        out = p.communicate()[0].decode()
+        if p.returncode:
+            raise RuntimeError("nvcc failed for %s:\n%s" % (name, out))
+        objs = [os.path.join(B.LIBDIR, s.replace(".cu", ".o")) if s != SRC else o for s in B.SOURCES]
+        subprocess.check_call([B._nvcc(), "-shared", "-o", lib] + objs)
+    return [os.path.join(B.LIBDIR, "libnfi_b200_%s.so" % n) for n in VARIANTS]
+
+
+if __name__ == "__main__":
+    print("\n".join(build(force="--force" in sys.argv)))
