@@ -82,6 +82,21 @@ int nfi_ray_bundle_bwd(const float* cam2world, const float* focal, int focal_str
 int nfi_near_far(const float* origins, const float* dirs, int64_t R, float scene_range,
                  float* near, float* far, void* workspace, nfi_stream_t stream);
 
+/* ---- A2 for callers that cannot allocate (CUDA-graph capture, tight serving loops, harnesses that
+ *      forbid cudaMalloc).  NO COUNTERPART IN THE REFERENCE.
+ *      Same kernels and same results as nfi_near_far, but the reduction
+ *      scratch is a file-scope `static __device__` array inside the library (NFI_NEARFAR_WS_BYTES =
+ *      16 KiB, held by every GPU that loads the library until the process exits) instead of a caller
+ *      workspace; the call performs no cudaMalloc / cudaFree and calls no allocating routine.
+ *      hits_out: DEVICE int32 [1] receiving the number of rays that hit the box, or NULL.
+ *      Limit: R <= NFI_NEARFAR_STATIC_MAX_RAYS, larger R is rejected with NFI_ERR_BAD_ARG.
+ *      All calls on one device share the one array: calls that may overlap on the GPU (different
+ *      streams without an ordering between them) RACE on it -- serialise them or use nfi_near_far.
+ *      Nothing in the array has to start at zero (each call writes every word it later reads). ---- */
+#define NFI_NEARFAR_STATIC_MAX_RAYS (1 << 24)
+int nfi_near_far_static(const float* origins, const float* dirs, int64_t R, float scene_range,
+                        float* near, float* far, int32_t* hits_out, nfi_stream_t stream);
+
 /* ---- A3: nerf_utils.compute_query_points_from_rays (lib/nerf_utils.py:96-122) ------------------
  * u [R,S] uniforms or NULL; randomize with u == NULL draws Philox4x32-10 numbers from (seed, offset). */
 int nfi_stratified(const float* near, const float* far, const float* u, int64_t R, int S,

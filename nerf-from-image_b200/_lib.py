@@ -51,6 +51,7 @@ _SIGS = {
     "nfi_ray_bundle_fwd": (c_int, [_P, _P, c_int, _P, _P, c_int, c_int, c_int, c_int, _P, _P, _P]),
     "nfi_ray_bundle_bwd": (c_int, [_P, _P, c_int, _P, _P, c_int, c_int, c_int, c_int, _P, _P, _P, _P, _P]),
     "nfi_near_far": (c_int, [_P, _P, c_int64, c_float, _P, _P, _P, _P]),
+    "nfi_near_far_static": (c_int, [_P, _P, c_int64, c_float, _P, _P, _P, _P]),
     "nfi_stratified": (c_int, [_P, _P, _P, c_int64, c_int, c_int, c_uint64, c_uint64, _P, _P]),
     "nfi_points_fwd": (c_int, [_P, _P, _P, c_int64, c_int, _P, _P]),
     "nfi_points_bwd": (c_int, [_P, _P, c_int64, c_int, _P, _P, _P]),
@@ -119,7 +120,7 @@ def stream_of(t):
 
 
 # kernels launched per C-ABI call (everything else launches exactly one)
-KERNELS_PER_CALL = {"nfi_near_far": 2}
+KERNELS_PER_CALL = {"nfi_near_far": 2, "nfi_near_far_static": 2}
 
 
 class LaunchProfile:

@@ -2,6 +2,8 @@
 // Replaces lib/nerf_utils.py:28-122, 227-275 (about 100 tiny ATen launches per render) with a
 // handful of streaming kernels.  All of these are HBM-bound elementwise work: one thread per
 // ray (or per sample), coalesced accesses, grids sized in multiples of the SM count.
+#include <mutex>
+
 #include "nfi_common.cuh"
 #include "nfi_math.cuh"
 
@@ -311,6 +313,63 @@ extern "C" int nfi_near_far(const float* origins, const float* dirs, int64_t R, 
   near_far_apply_kernel<<<grid_for(R, kThreads), kThreads, 0, nfi_cu(stream)>>>(
       origins, dirs, R, scene_range, nb, pmin, pmax, pcnt, hits, near, far);
   NFI_CHECK_LAUNCH("near_far_apply_kernel");
+  return NFI_OK;
+}
+
+// ------------------------------------------------------------------------------------------
+// A2 without allocation: the partials of the two-pass reduction live in a file-scope device array
+// instead of a caller workspace.  No counterpart in the reference (see include/nfi_b200.h).
+// The array's name is only a host-side stand-in in host code: its device address is looked up once
+// per device with cudaGetSymbolAddress (that device current) and passed to the kernels.
+// ------------------------------------------------------------------------------------------
+static __device__ __align__(256) unsigned char g_near_far_static_scratch[NFI_NEARFAR_WS_BYTES];
+
+static int near_far_static_scratch(void** out) {
+  constexpr int kMaxDev = 64;
+  static std::mutex mu;
+  static void* addr[kMaxDev];           // zero-initialised: NULL = not looked up yet on that device
+  int dev = -1;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess)
+    return nfi_set_error(NFI_ERR_LAUNCH, "nfi_near_far_static: cudaGetDevice: %s", cudaGetErrorString(e));
+  NFI_REQUIRE(dev >= 0 && dev < kMaxDev, NFI_ERR_UNSUPPORTED, "nfi_near_far_static: device id %d >= %d", dev, kMaxDev);
+  std::lock_guard<std::mutex> lock(mu);
+  if (!addr[dev]) {
+    void* p = nullptr;
+    e = cudaGetSymbolAddress(&p, g_near_far_static_scratch);
+    if (e != cudaSuccess || !p)
+      return nfi_set_error(NFI_ERR_LAUNCH, "nfi_near_far_static: cudaGetSymbolAddress on device %d: %s", dev,
+                           cudaGetErrorString(e));
+    addr[dev] = p;
+  }
+  *out = addr[dev];
+  return NFI_OK;
+}
+
+extern "C" int nfi_near_far_static(const float* origins, const float* dirs, int64_t R, float scene_range,
+                                   float* near, float* far, int32_t* hits_out, nfi_stream_t stream) {
+  NFI_REQUIRE(origins && dirs && near && far, NFI_ERR_BAD_ARG, "nfi_near_far_static: NULL pointer");
+  NFI_REQUIRE(R > 0, NFI_ERR_BAD_ARG, "nfi_near_far_static: R must be positive");
+  NFI_REQUIRE(R <= (int64_t)NFI_NEARFAR_STATIC_MAX_RAYS, NFI_ERR_BAD_ARG,
+              "nfi_near_far_static: R = %lld rays exceeds NFI_NEARFAR_STATIC_MAX_RAYS = %lld; use nfi_near_far "
+              "with a caller workspace", (long long)R, (long long)NFI_NEARFAR_STATIC_MAX_RAYS);
+  static_assert(8 + kMaxBlocks * 12 <= NFI_NEARFAR_WS_BYTES, "static scratch too small");
+  void* scratch = nullptr;
+  const int rc = near_far_static_scratch(&scratch);
+  if (rc != NFI_OK) return rc;
+  // every word the second pass reads ([0, nb) of each partial array) is written by the first pass of
+  // THIS call, so nothing left over from an earlier call is ever consumed and nothing needs zeroing
+  int* hits = hits_out ? (int*)hits_out : (int*)scratch;
+  float* pmin = (float*)scratch + 2;
+  float* pmax = pmin + kMaxBlocks;
+  int* pcnt = (int*)(pmax + kMaxBlocks);
+  int nb = grid_for(R, kThreads);
+  if (nb > kMaxBlocks) nb = kMaxBlocks;
+  near_far_reduce_kernel<<<nb, kThreads, 0, nfi_cu(stream)>>>(origins, dirs, R, scene_range, pmin, pmax, pcnt);
+  NFI_CHECK_LAUNCH("near_far_reduce_kernel (static scratch)");
+  near_far_apply_kernel<<<grid_for(R, kThreads), kThreads, 0, nfi_cu(stream)>>>(
+      origins, dirs, R, scene_range, nb, pmin, pmax, pcnt, hits, near, far);
+  NFI_CHECK_LAUNCH("near_far_apply_kernel (static scratch)");
   return NFI_OK;
 }
 
