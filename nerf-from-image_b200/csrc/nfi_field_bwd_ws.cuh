@@ -51,6 +51,7 @@
 // the gather's wait unconditional would open the mirror-image race (scatter arriving on s_free for an
 // idle tile before a slow gather warp has tested the previous phase), so BOTH waits are unconditional.
 #pragma once
+#include "nfi_f2.cuh"
 #include "nfi_field_tc.cuh"
 
 namespace nfi_ftc {
@@ -244,6 +245,11 @@ __device__ __forceinline__ float4 bw_weights(const float4& d) {
 // Texel order: 0 (x0,y0)  1 (x1,y0)  2 (x0,y1)  3 (x1,y1).
 //   dF/d ix = (v1 - v0) + ((v3 - v2) - (v1 - v0)) ty      dF/d iy = (v2 - v0) + ((v3 - v1) - (v2 - v0)) tx
 // (texel differences first: sums of the raw texels cancel to ~1e-4 relative in the pose gradient)
+// Round-2 A/B (config 2, ms per launch, same box): this scalar form 6.78; the same operations as packed
+// FADD2 / FFMA2 pairs (nfi_f2.cuh) 7.18; the factored form F = v0 + tx dF/dix + ty (v2 - v0), packed or
+// scalar, 7.24 / 7.47 -- both need more live registers, and at the 96-register cap of this 17-warp CTA
+// ptxas then spills inside this loop (320 instead of 144 bytes of spill loads).  The packed form is kept
+// where registers allow it: the scatter below and the forward gather (126 registers).
 template <bool WANT_PTS, bool BF16>
 __device__ __forceinline__ void bw_gather(const Args& a, const BwTable& tb, float* a_hi, float* a_lo, float* tq,
                                           int b, int w, int lane) {
@@ -323,17 +329,18 @@ __device__ __forceinline__ void bw_scatter_rows(const Args& a, const BwTable& tb
     const int sl = it * 4 + (lane >> 3);
     const int s = row0 + sl;
     if (tb.keep[s] >= 0.f) {
-      float4 g = *reinterpret_cast<const float4*>(&df[sl * kBwDfLd + c4 * 4]);
-      g.x *= third; g.y *= third; g.z *= third; g.w *= third;
+      using namespace nfi_f2;
+      const f4 g = mul(from4(*reinterpret_cast<const float4*>(&df[sl * kBwDfLd + c4 * 4])), third);
 #pragma unroll
       for (int p = 0; p < 3; ++p) {
         // a clamped neighbour (x1 == x0 at the border) carries weight 0: adding 0 is harmless
         const uint4 o = tb.toff[p][s];
         const float4 wt = bw_weights(tb.tder[p][s]);
-        red_add_v4(reinterpret_cast<float*>(gbase + o.x), g.x * wt.x, g.y * wt.x, g.z * wt.x, g.w * wt.x);
-        red_add_v4(reinterpret_cast<float*>(gbase + o.y), g.x * wt.y, g.y * wt.y, g.z * wt.y, g.w * wt.y);
-        red_add_v4(reinterpret_cast<float*>(gbase + o.z), g.x * wt.z, g.y * wt.z, g.z * wt.z, g.w * wt.z);
-        red_add_v4(reinterpret_cast<float*>(gbase + o.w), g.x * wt.w, g.y * wt.w, g.z * wt.w, g.w * wt.w);
+        const float4 r0 = to4(mul(g, wt.x)), r1 = to4(mul(g, wt.y)), r2 = to4(mul(g, wt.z)), r3 = to4(mul(g, wt.w));
+        red_add_v4(reinterpret_cast<float*>(gbase + o.x), r0.x, r0.y, r0.z, r0.w);
+        red_add_v4(reinterpret_cast<float*>(gbase + o.y), r1.x, r1.y, r1.z, r1.w);
+        red_add_v4(reinterpret_cast<float*>(gbase + o.z), r2.x, r2.y, r2.z, r2.w);
+        red_add_v4(reinterpret_cast<float*>(gbase + o.w), r3.x, r3.y, r3.z, r3.w);
       }
     }
   }

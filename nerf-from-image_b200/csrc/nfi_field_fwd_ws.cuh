@@ -17,6 +17,7 @@
 //   d1_full[c]    MMA(commit) -> E      layer 1 accumulators complete (also: H of set c is free again)
 //   meta_empty[m] E -> P                table m no longer needed
 #pragma once
+#include "nfi_f2.cuh"
 #include "nfi_field_tc.cuh"
 
 namespace nfi_ftc {
@@ -164,8 +165,9 @@ __device__ __forceinline__ void ws_gather(const Args& a, const WsTables& tb, con
                      (int64_t)b * 3 * a.Hp * a.Wp * (BF16 ? 64 : 128) + c4 * (BF16 ? 8 : 16);
 #pragma unroll 2
   for (int it = 0; it < kWsRows / 4; ++it) {
+    using namespace nfi_f2;
     const int s = gw * kWsRows + it * 4 + (lane >> 3);
-    float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+    f4 acc = zero4();
     if (sample_active(a, mt.keep[s])) {
       float4 v[3][4];
       float4 w[3];
@@ -177,12 +179,12 @@ __device__ __forceinline__ void ws_gather(const Args& a, const WsTables& tb, con
         v[p][2] = ldg_texel4<BF16>(base, o.z); v[p][3] = ldg_texel4<BF16>(base, o.w);
       }
 #pragma unroll
-      for (int p = 0; p < 3; ++p) {
-        ws_fma4(acc, v[p][0], w[p].x); ws_fma4(acc, v[p][1], w[p].y);
-        ws_fma4(acc, v[p][2], w[p].z); ws_fma4(acc, v[p][3], w[p].w);
+      for (int p = 0; p < 3; ++p) {       // same order and rounding as the scalar form, two channels per FFMA2
+        acc = fma(from4(v[p][0]), w[p].x, acc); acc = fma(from4(v[p][1]), w[p].y, acc);
+        acc = fma(from4(v[p][2]), w[p].z, acc); acc = fma(from4(v[p][3]), w[p].w, acc);
       }
     }
-    nfi_mlp::store_feat4(a_hi, a_lo, s, c4, acc);
+    nfi_mlp::store_feat4(a_hi, a_lo, s, c4, to4(acc));
   }
 }
 

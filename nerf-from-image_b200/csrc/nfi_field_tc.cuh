@@ -38,6 +38,7 @@ struct Args {
   int64_t n_total;        // B * npi * S samples
   int64_t tiles_per_image;
   int blocks_x;           // pixel-block order: blocks per image row (0 = linear order)
+  float inv_S, inv_bx;    // 1 / S, 1 / blocks_x for fast_div (tile -> pixel block / depth step without IDIV sequences)
   float* out; float* probs;
   // backward
   const float* g_out;
@@ -57,22 +58,33 @@ __device__ __forceinline__ float4 ldg_texel4(const char* base, uint32_t off) {
   return __ldg(reinterpret_cast<const float4*>(base + off));
 }
 
+// n / d for 0 <= n < 2^24, d >= 1, inv = 1.f / d: the float product is within one of the quotient (n is
+// exact in fp32), one correction step makes it exact.  Replaces the ~20-instruction integer division
+// sequences that ran once per row and tile in every producer warp.
+__device__ __forceinline__ int fast_div(int n, int d, float inv) {
+  int q = __float2int_rz(__int2float_rn(n) * inv);
+  const int r = n - q * d;
+  q += (r >= d) ? 1 : 0;
+  q -= (r < 0) ? 1 : 0;
+  return q;
+}
+
 // (tile-in-image, thread) -> sample index WITHIN the image (ray_in_image * S + k), or -1.
-// 32-bit arithmetic: fill_args guarantees npi * S < 2^31.
+// 32-bit arithmetic: fill_args guarantees npi * S < 2^31 (so tile indices are < 2^24).
 __device__ __forceinline__ int sample_in_image(const Args& a, int t, int tid) {
   if (a.blocks_x == 0) {
     const int64_t local = (int64_t)t * kTile + tid;
     return local < a.npi * a.S ? (int)local : -1;
   }
-  const int blk = t / a.S;                     // depth step fastest: consecutive tiles share texels
+  const int blk = fast_div(t, a.S, a.inv_S);   // depth step fastest: consecutive tiles share texels
   const int k = t - blk * a.S;
-  const int by = blk / a.blocks_x, bx = blk - by * a.blocks_x;
+  const int by = fast_div(blk, a.blocks_x, a.inv_bx), bx = blk - by * a.blocks_x;
   const int py = tid >> 4, px = tid & 15;
   const int ray = (by * 8 + py) * a.img_w + bx * 16 + px;
   return ray * a.S + k;
 }
 
-// same mapping, also returning the ray index within the image (no 64-bit division on the hot path)
+// same mapping, also returning the ray index within the image
 __device__ __forceinline__ int sample_and_ray(const Args& a, int t, int tid, int& ray) {
   if (a.blocks_x == 0) {
     const int64_t local = (int64_t)t * kTile + tid;
@@ -80,9 +92,9 @@ __device__ __forceinline__ int sample_and_ray(const Args& a, int t, int tid, int
     ray = (int)local / a.S;
     return (int)local;
   }
-  const int blk = t / a.S;
+  const int blk = fast_div(t, a.S, a.inv_S);
   const int k = t - blk * a.S;
-  const int by = blk / a.blocks_x, bx = blk - by * a.blocks_x;
+  const int by = fast_div(blk, a.blocks_x, a.inv_bx), bx = blk - by * a.blocks_x;
   const int py = tid >> 4, px = tid & 15;
   ray = (by * 8 + py) * a.img_w + bx * 16 + px;
   return ray * a.S + k;

@@ -41,6 +41,8 @@ static inline int fill_args(Args& a, const char* who, const NfiField* field, con
   if (!points && img_w > 0 && n_per_image % img_w == 0 && img_w % 16 == 0 && (n_per_image / img_w) % 8 == 0) {
     a.blocks_x = img_w / 16;                      // per_image is then a multiple of 128
   }
+  a.inv_S = 1.f / (float)S;
+  a.inv_bx = a.blocks_x > 0 ? 1.f / (float)a.blocks_x : 1.f;
   a.out = nullptr; a.probs = nullptr; a.g_out = nullptr;
   a.g_planes = a.g_palette = a.g_points = a.g_params = nullptr;
   return NFI_OK;

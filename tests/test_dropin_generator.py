@@ -259,5 +259,8 @@ def test_make_render_two_threads_two_streams(cuda_setup):
     for i in range(2):
         for k in ("rgb", "depth", "mask"):     # not bitwise: cuDNN may pick another algorithm per stream / handle
             assert rel_err(results[i][k].cpu(), solo[i][k].cpu()) < 1e-5, (i, k)
-        for k in ("d_ws", "d_cam", "d_focal"):
-            assert rel_err(results[i][k].cpu(), solo[i][k].cpu()) < TOL, (i, k)
+        # the planes themselves differ in the last bits between the two runs (cuDNN picks per stream), and the
+        # pose gradient is the quantity that sees importance-bin flips (POSE_TOL in test_gpu_parity.py)
+        assert rel_err(results[i]["d_ws"].cpu(), solo[i]["d_ws"].cpu()) < TOL, i
+        for k in ("d_cam", "d_focal"):
+            assert rel_err(results[i][k].cpu(), solo[i][k].cpu()) < 5e-3, (i, k)
