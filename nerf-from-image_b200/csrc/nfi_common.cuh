@@ -27,3 +27,7 @@ static inline cudaStream_t nfi_cu(nfi_stream_t s) { return (cudaStream_t)s; }
 
 // number of SMs of the *current* device, cached per device id (read-only after first use)
 int nfi_sm_count();
+
+// cudaFuncSetAttribute(kernel, MaxDynamicSharedMemorySize, bytes) once per (kernel, device) instead of on
+// every launch (per-device set-up is done once).  Thread-safe; returns NFI_OK or NFI_ERR_LAUNCH.
+int nfi_set_smem_once(const void* kernel, int bytes, const char* who);

@@ -383,10 +383,8 @@ extern "C" int nfi_field_bwd(const NfiField* field, const float* planes_cl, cons
     const int smem = (int)sizeof(BwSmem);
 #define NFI_LAUNCH_BWS1(P, M, W, H)                                                                     \
   do {                                                                                                  \
-    cudaError_t e = cudaFuncSetAttribute(field_bwd_ws_kernel<P, M, W, H>,                               \
-                                         cudaFuncAttributeMaxDynamicSharedMemorySize, smem);            \
-    NFI_REQUIRE(e == cudaSuccess, NFI_ERR_LAUNCH, "nfi_field_bwd: cudaFuncSetAttribute: %s",            \
-                cudaGetErrorString(e));                                                                 \
+    const int rc_ = nfi_set_smem_once((const void*)field_bwd_ws_kernel<P, M, W, H>, smem, "nfi_field_bwd"); \
+    if (rc_) return rc_;                                                                                \
     field_bwd_ws_kernel<P, M, W, H><<<grid, kBwThreads, smem, st>>>(a);                                 \
   } while (0)
 #define NFI_LAUNCH_BWS(P, M, W)                                                                         \
@@ -428,10 +426,8 @@ extern "C" int nfi_field_bwd(const NfiField* field, const float* planes_cl, cons
   const int smem = (int)sizeof(BwdSmemW);
 #define NFI_LAUNCH_BWD(P, M, W)                                                                         \
   do {                                                                                                  \
-    cudaError_t e = cudaFuncSetAttribute(field_bwd_tc_kernel<P, M, W, true>,                            \
-                                         cudaFuncAttributeMaxDynamicSharedMemorySize, smem);            \
-    NFI_REQUIRE(e == cudaSuccess, NFI_ERR_LAUNCH, "nfi_field_bwd: cudaFuncSetAttribute: %s",            \
-                cudaGetErrorString(e));                                                                 \
+    const int rc_ = nfi_set_smem_once((const void*)field_bwd_tc_kernel<P, M, W, true>, smem, "nfi_field_bwd"); \
+    if (rc_) return rc_;                                                                                \
     field_bwd_tc_kernel<P, M, W, true><<<grid, kThreads, smem, st>>>(a);                                \
   } while (0)
   if (points) {

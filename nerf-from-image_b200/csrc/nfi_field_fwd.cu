@@ -83,9 +83,7 @@ void launch_plane_transpose(const float* src, float* dst, int B, int HW, int Wp,
 
 template <typename K>
 int set_smem(K kernel, int bytes, const char* who) {
-  cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
-  NFI_REQUIRE(e == cudaSuccess, NFI_ERR_LAUNCH, "%s: cudaFuncSetAttribute: %s", who, cudaGetErrorString(e));
-  return NFI_OK;
+  return nfi_set_smem_once((const void*)kernel, bytes, who);
 }
 
 }  // namespace

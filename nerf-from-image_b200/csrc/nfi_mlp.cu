@@ -85,8 +85,8 @@ extern "C" int nfi_decoder_mlp_fwd(const NfiField* field, const float* feat, int
   NFI_REQUIRE(n > 0 && field->n_out >= 1 && field->n_out <= NFI_MAX_OUT, NFI_ERR_BAD_ARG, "nfi_decoder_mlp_fwd: bad sizes");
   NFI_REQUIRE(nfi_aligned16(feat), NFI_ERR_ALIGNMENT, "nfi_decoder_mlp_fwd: feat must be 16-byte aligned");
   const int smem = (int)sizeof(Operands);
-  cudaError_t e = cudaFuncSetAttribute(decoder_mlp_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
-  NFI_REQUIRE(e == cudaSuccess, NFI_ERR_LAUNCH, "nfi_decoder_mlp_fwd: cudaFuncSetAttribute: %s", cudaGetErrorString(e));
+  const int rc = nfi_set_smem_once((const void*)decoder_mlp_fwd_kernel, smem, "nfi_decoder_mlp_fwd");
+  if (rc) return rc;
   const int64_t n_tiles = (n + kTile - 1) / kTile;
   const int64_t cap = (int64_t)nfi_sm_count() * 2;
   const int grid = (int)(n_tiles < cap ? n_tiles : cap);

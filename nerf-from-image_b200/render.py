@@ -25,7 +25,7 @@ def render_planes(planes, palette, field: Field, height: int, width: int, tform_
                   planes_layout: str = "nchw", u_strat=None, u_pdf=None, check_hits=True,
                   return_aux: bool = False, compute_normals: bool = False,
                   compute_semantics: bool = False, compute_coords: bool = False,
-                  plane_dtype: torch.dtype = torch.float32):
+                  plane_dtype: torch.dtype = torch.float32, z_fine=None):
     """Render `B` images.  planes: [B,96,Hp,Wp] or [B,3,32,Hp,Wp] (layout 'nchw', the StyleGAN2
     output of models/generator.py:475-477) or [B,3,Hp,Wp,32] ('cl').  palette: attention values
     [B,A,3] (None for the plain RGB head).  Returns (rgb [B,H,W,3], depth [B,H,W], mask [B,H,W])
@@ -36,7 +36,9 @@ def render_planes(planes, palette, field: Field, height: int, width: int, tform_
     the semantics slot, run.py:337-338); they imply `return_aux`.
     plane_dtype=torch.bfloat16 is the bf16 mode of the contract (1e-2 instead of 1e-4): the gather reads
     a bfloat16 copy of the planes (half the texel bytes); everything after the load, and every gradient,
-    stays fp32.  Not available together with decoder weight gradients or the extra maps."""
+    stays fp32.  Not available together with decoder weight gradients or the extra maps.
+    z_fine [B,H,W,S] (test hook): use these fine depths instead of running A7 + A8 -- lets a parity test
+    feed the reference's own importance samples, so that what remains is the differentiable path alone."""
     H, W, S = int(height), int(width), int(depth_samples_per_ray)
     cam = tform_cam2world
     B = cam.shape[0]
@@ -74,7 +76,10 @@ def render_planes(planes, palette, field: Field, height: int, width: int, tform_
         # A7 + A8 (no_grad, run.py:261-281)
         if randomize and u_pdf is None:
             u_pdf = torch.rand((B * H * W, S), dtype=torch.float32, device=dev)
-        z_f = ops.importance(coarse, d, z_c, u_pdf if randomize else None, sigma_stride=4)
+        if z_fine is None:
+            z_f = ops.importance(coarse, d, z_c, u_pdf if randomize else None, sigma_stride=4)
+        else:
+            z_f = z_fine.detach().reshape(z_c.shape).contiguous().float()
         fine, probs_f = ops.field_on_rays(planes_cl, palette, *wts, o_s, d_s, z_f, field.cfg, img_w=W,
                                           skip_oob=not want_sem, want_probs=want_sem, sink=sink, planes_bf16=pl16)
         # A9 + A10
