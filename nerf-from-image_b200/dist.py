@@ -66,26 +66,66 @@ def gather_report(local: torch.Tensor, batch: int) -> torch.Tensor:
     return torch.cat([p[: b - a] for p, (a, b) in zip(parts, sizes)], dim=0)
 
 
-def allreduce_grads(grads: Sequence[Optional[torch.Tensor]], batch_weight: Optional[float] = None):
+def _collective_device(tensors) -> torch.device:
+    for t in tensors:
+        if t is not None:
+            return t.device
+    if dist.get_backend() == "nccl":
+        return torch.device("cuda", torch.cuda.current_device())
+    return torch.device("cpu")
+
+
+def allreduce_grads(grads: Sequence[Optional[torch.Tensor]], batch_weight: Optional[float] = None,
+                    params: Optional[Sequence[torch.Tensor]] = None):
     """Sum the gradients of parameters shared by all images (decoder W0/b0/W1/b1, beta, alpha) over the
-    ranks, in place, as ONE flat bucket (they are ~2.7 k floats in total: one collective of launch-latency
-    size, not one per tensor).  nn.DataParallel sums replica gradients (run.py:636-644), so the default is
-    a plain sum; `batch_weight` scales the result (e.g. 1 / world for a mean).  None entries are skipped."""
+    ranks as ONE flat bucket (they are ~2.7 k floats in total: one collective of launch-latency size, not
+    one per tensor).  nn.DataParallel sums replica gradients (run.py:636-644), so the default is a plain
+    sum; `batch_weight` scales the result (e.g. 1 / world for a mean).
+
+    Every rank always enters the same two collectives with buffers of identical length, whatever it holds:
+    a rank that owns no image (shard_range allows batch < world) passes None for everything and contributes
+    zeros.  The bucket layout comes from `params` (same list on every rank) when given, else from a MAX
+    all-reduce of the per-entry element counts.  Returns a list: live entries are reduced in place, entries
+    that were None here but live on another rank come back as new tensors (shaped like `params[i]`, or flat),
+    entries that are None on every rank stay None."""
     rank, world = rank_world()
-    live = [g for g in grads if g is not None]
-    if world == 1 or not live:
+    grads = list(grads)
+    if params is not None and len(params) != len(grads):
+        raise ValueError("allreduce_grads: %d gradients for %d parameters" % (len(grads), len(params)))
+    if world == 1:
         if batch_weight is not None:
-            for g in live:
-                g.mul_(batch_weight)
+            for g in grads:
+                if g is not None:
+                    g.mul_(batch_weight)
         return grads
-    flat = torch.cat([g.reshape(-1).to(torch.float32) for g in live])
+    dev = _collective_device(list(grads) + list(params or []))
+    if params is not None:
+        sizes = [int(p.numel()) for p in params]
+    else:
+        t = torch.tensor([0 if g is None else g.numel() for g in grads], dtype=torch.int64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        sizes = [int(v) for v in t.tolist()]
+    for g, n in zip(grads, sizes):
+        if g is not None and g.numel() != n:
+            raise ValueError("allreduce_grads: a gradient has %d elements here, %d elsewhere" % (g.numel(), n))
+    flat = torch.zeros(sum(sizes), dtype=torch.float32, device=dev)
+    off = 0
+    for g, n in zip(grads, sizes):
+        if g is not None:
+            flat[off:off + n] = g.reshape(-1).to(torch.float32)
+        off += n
     dist.all_reduce(flat, op=dist.ReduceOp.SUM)
     if batch_weight is not None:
         flat.mul_(batch_weight)
     off = 0
-    for g in live:
-        n = g.numel()
-        g.copy_(flat[off:off + n].view_as(g))
+    for i, (g, n) in enumerate(zip(grads, sizes)):
+        if n == 0:
+            continue
+        if g is not None:
+            g.copy_(flat[off:off + n].view_as(g))
+        else:
+            piece = flat[off:off + n].clone()
+            grads[i] = piece.view_as(params[i]) if params is not None else piece
         off += n
     return grads
 

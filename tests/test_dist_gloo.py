@@ -63,6 +63,16 @@ def _worker(rank, world, port, batch, q):
         ok = ok and grads[1] is None and torch.equal(grads[0], pats[0] * tot) and torch.equal(grads[2], pats[2] * tot)
         nd.allreduce_grads(grads, batch_weight=1.0 / world)
         ok = ok and torch.allclose(grads[0], pats[0] * tot)      # mean of equal contributions
+        # a rank that owns no image (batch < world) passes None for everything and must still enter the same
+        # collectives: rank 1 contributes nothing, both ranks end with rank 0's gradients
+        mine = [p.clone() if (p is not None and rank == 0) else None for p in pats]
+        out = nd.allreduce_grads(mine)
+        ok = ok and out[1] is None and torch.equal(out[0].reshape(2, 3), pats[0]) and torch.equal(out[2], pats[2])
+        shapes = [torch.empty(2, 3), torch.empty(5), torch.empty(4)]
+        mine = [pats[0].clone() if rank == 0 else None, None, pats[2].clone() if rank == 1 else None]
+        out = nd.allreduce_grads(mine, params=shapes)
+        ok = ok and out[0].shape == (2, 3) and torch.equal(out[0], pats[0]) and torch.equal(out[2], pats[2])
+        ok = ok and out[1].shape == (5,) and float(out[1].abs().sum()) == 0.0
         q.put((rank, bool(ok), t))
     finally:
         dist.destroy_process_group()
