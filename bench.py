@@ -1,14 +1,15 @@
 #!/usr/bin/env python
-"""bench.py -- rays/s (fwd+bwd) of the volume-rendering hot path on N B200s (weak scaling, no
-data-path collective: images are independent).
+"""bench.py -- rays/s of the volume-rendering hot path on N B200s (no data-path collective: images are
+independent).
 
-    python bench.py --gpus N --steps K --warmup W            # this repo's CUDA path
-    python bench.py --impl reference --steps K --warmup W    # CPU arm (oracle port of the reference)
+    python bench.py --gpus N --steps K --warmup W                  # this repo's CUDA path, config 2
+    python bench.py --config {1,2,3s,3c,4,5} ...                    # the other BASELINE.json configs
+    python bench.py --impl reference --steps K --warmup W           # the reference's own CPU path
 
-A step = one render forward + backward (loss = the reference's l1 branch, run.py:2236-2238) over
-one batch of synthetic inputs of BASELINE.json config 2: 16 images, 128x128 rays each, 64 coarse +
-64 fine samples per ray, perspective cameras, gradients to planes, attention values, cam2world and
-focal.  Prints ONE JSON line (rank 0).
+A step = one pass of the hot path over one batch of synthetic inputs of the chosen BASELINE.json config
+(default 2: 16 images, 128x128 rays each, 64 coarse + 64 fine samples per ray, perspective cameras, render
+forward + l1 loss (run.py:2236-2238) + backward to planes, attention values, cam2world and focal).
+Prints ONE JSON line (rank 0).
 """
 import argparse
 import json
@@ -27,8 +28,38 @@ import torch  # noqa: E402
 
 METRIC = "rays/sec (fwd+bwd)"
 UNIT = "rays/s"
-SCENE_RANGE = 1.4
 PLANE_BYTES = 3 * 32 * 256 * 256 * 4          # P, bytes per image
+S = 64                                         # depth_samples_per_ray (run.py:512)
+
+# BASELINE.json configs.  B = images per GPU ("weak") or in total over all ranks ("strong").
+CONFIGS = {
+    "1": dict(label="config1: p3d_car forward render, 1 image 64x64 rays, orthographic, deterministic depths",
+              B=1, res=64, camera="ortho", scene_range=1.4, white=False, backward=False, randomize=False,
+              grads=(), scaling="weak"),
+    "2": dict(label="config2: p3d_car inversion render fwd+bwd, perspective, grads to planes/attention/cam/focal",
+              B=16, res=128, camera="persp", scene_range=1.4, white=False, backward=True, randomize=True,
+              grads=("planes", "palette", "cam", "focal"), scaling="weak"),
+    "3s": dict(label="config3 (ShapeNet chairs): inversion fwd+bwd, batch 32 IN TOTAL sharded over the ranks, perspective, "
+                     "scene_range 0.55, white background, one focal value for all images, no pose gradient "
+                     "(data/loaders.py:120-123, 426-435)",
+               B=32, res=128, camera="persp_shared_focal", scene_range=0.55, white=True, backward=True,
+               randomize=True, grads=("planes", "palette"), scaling="strong"),
+    "3c": dict(label="config3 (CUB): inversion fwd+bwd, batch 32 IN TOTAL sharded over the ranks, orthographic cameras with "
+                     "T[3,3] != 1 (data/datasets.py:556-567), scene_range 2.0, grads to planes/attention/cam",
+               B=32, res=128, camera="cub", scene_range=2.0, white=False, backward=True, randomize=True,
+               grads=("planes", "palette", "cam"), scaling="strong"),
+    "4": dict(label="config4: perspective eval path (eval_kitti_persp.py:706, 948-950, 221-228): 1 image, 0-dim focal, "
+                    "principal point, z-buffer depth, scene_range 3.0, white background, fwd+bwd incl. pose",
+              B=1, res=128, camera="persp_eval", scene_range=3.0, white=True, backward=True, randomize=True,
+              grads=("planes", "palette", "cam", "focal"), zbuffer=True, scaling="weak"),
+    "5": dict(label="config5: generator-training gradient set (planes, attention, W0, b0, W1, b1, beta, alpha; run.py:980-986), "
+                    "4 images per GPU (batch 32 at 8 GPUs) + all-reduce of the generator's 32 164 056 and the discriminator's "
+                    "28 921 344 fp32 gradients over NCCL when more than one rank runs",
+              B=4, res=128, camera="persp", scene_range=1.4, white=False, backward=True, randomize=True,
+              grads=("planes", "palette", "W0", "b0", "W1", "b1", "beta", "alpha"), scaling="weak",
+              allreduce=(32164056, 28921344)),
+}
+WKEYS = ("W0", "b0", "W1", "b1", "beta", "alpha")
 
 
 def peaks():
@@ -74,19 +105,58 @@ class ClockSampler(threading.Thread):
                 "reasons": reasons, "samples": len(sm)}
 
 
-NCU_BWD_DRAM_BYTES = 1204762000 + 596777728      # launch 10 of profiles/r01z_field_ws_ncu_full_summary.txt
+# ncu --set full capture of one field_bwd launch at config 2 (dram__bytes_read.sum + dram__bytes_write.sum)
+NCU_BWD_DRAM = {"bytes": None, "source": None}
+try:
+    with open(os.path.join(ROOT, "profiles", "r02_bwd_dram_bytes.json")) as _f:
+        NCU_BWD_DRAM = json.load(_f)
+except Exception:
+    NCU_BWD_DRAM = {"bytes": 1204762000 + 596777728, "source": "profiles/r01z_field_ws_ncu_full_summary.txt"}
 
 
-def make_inputs(B, H, W, S, seed_shift=0):
-    """Synthetic config-2 inputs on the CPU: smooth planes, calibrated decoder,
-    random object-centred perspective poses, l1 target."""
+def make_inputs(cfg, B, seed_shift=0, res=None):
+    """Synthetic inputs of one config on the CPU: smooth 256x256 planes, decoder calibrated so
+    that the mask is non-trivial, random object-centred cameras of the config's model, l1 target.
+    Returns a dict of CPU tensors: planes, palette, cam, focal (None / [B] / 0-dim), center (None / [B,2]),
+    target, and the decoder dict `field`."""
     from nfi_b200 import synth
+    H = W = res or cfg["res"]
     planes = synth.make_planes(B, res=256, seed=1 + seed_shift)
     fd = synth.make_field(planes, seed=3)
     pal = synth.make_palette(B, 10, seed=4 + seed_shift)
-    cam, focal = synth.make_cameras(B, seed=2 + seed_shift, perspective=True)
+    kind = cfg["camera"]
+    center = None
+    if kind == "cub":
+        cam, focal = synth.make_ortho_cub_cameras(B, seed=7 + seed_shift), None
+    elif kind == "ortho":
+        cam, focal = synth.make_cameras(B, seed=5 + seed_shift, perspective=False)
+    else:
+        cam, focal = synth.make_cameras(B, seed=2 + seed_shift, perspective=True)
+        cam = cam.clone()
+        cam[:, :3, 3] *= cfg["scene_range"] / 1.4            # keep the box at the same apparent size
+        if kind == "persp_shared_focal":                      # data/loaders.py:426-435: one focal, expanded
+            focal = focal[:1].expand(B).contiguous()
+        elif kind == "persp_eval":                            # eval_kitti_persp.py:948-950
+            focal = focal[0].clone()                          # 0-dim
+            center = 0.5 + (torch.rand(B, 2, generator=torch.Generator().manual_seed(11 + seed_shift)) - 0.5) * 0.1
     target = torch.rand(B, H, W, 3, generator=torch.Generator().manual_seed(7 + seed_shift)) * 2 - 1
-    return planes, fd, pal, cam, focal, target
+    return dict(planes=planes, palette=pal, cam=cam, focal=focal, center=center, target=target, field=fd)
+
+
+def auto_chunks(B):
+    """Image chunks of the pipelined end-to-end leg: short first / last chunks (their copy-in / copy-out overlaps
+    nothing), 4-image chunks between (sweep on one B200, ms per step at B=16: 8x2 23.5 | 1,1,4,4,4,1,1 22.6 |
+    1,3,4,4,3,1 22.4).  Small batches go as one chunk."""
+    if B < 8:
+        return [B]
+    mid, n_chunks = B - 2, [1]
+    while mid > 0:
+        n_chunks.append(min(4, mid) if mid not in (5, 6, 7) else 3)
+        mid -= n_chunks[-1]
+    left, right = [], []
+    for i, v in enumerate(sorted(n_chunks[1:])):        # smaller chunks towards the two ends
+        (left if i % 2 == 0 else right).append(v)
+    return [1] + left + right[::-1] + [1]
 
 
 # ---------------------------------------------------------------------------------------------
@@ -95,6 +165,8 @@ def make_inputs(B, H, W, S, seed_shift=0):
 def run_ours(args):
     import torch.distributed as dist
     from nfi_b200 import _lib, decoder, render
+    from nfi_b200.dist import shard_range
+    cfg = CONFIGS[args.config]
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
@@ -104,36 +176,75 @@ def run_ours(args):
     if world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         dist.init_process_group("nccl", device_id=dev)
-        # host-side group for the end-to-end leg's barriers and the final reductions: they must still work
-        # on a rank whose CUDA context died in that leg (see the guard below)
-        host_group = dist.new_group(backend="gloo")
     _lib.lib()
-    B, H, W, S = args.batch, args.res, args.res, 64
+    B_cfg = args.batch or cfg["B"]
+    if cfg["scaling"] == "strong":                 # fixed total batch, sharded by image (dist.shard_range)
+        lo, hi = shard_range(B_cfg, rank, world)
+        B, B_total = hi - lo, B_cfg
+    else:
+        B, B_total = B_cfg, B_cfg * world
+    assert B > 0, "more ranks than images"
+    H = W = args.res or cfg["res"]
     R = B * H * W
-    planes_h, fd, pal_h, cam_h, focal_h, target_h = make_inputs(B, H, W, S, seed_shift=rank)
-    fld = decoder.Field(*[fd[k].to(dev) for k in ("W0", "b0", "W1", "b1", "beta", "alpha")],
-                        SCENE_RANGE, 10, True)
-
+    inp = make_inputs(cfg, B, seed_shift=rank, res=H)
+    fd = inp["field"]
+    want = cfg["grads"]
+    backward = cfg["backward"]
     pdt = torch.bfloat16 if args.plane_dtype == "bf16" else torch.float32
+    wdev = {k: fd[k].to(dev).requires_grad_(k in want) for k in WKEYS}
+    fld = decoder.Field(*[wdev[k] for k in WKEYS], cfg["scene_range"], 10, True)
+    no_cam = backward and "cam" not in want
+    names = [k for k in ("planes", "palette", "cam", "focal", "center", "target") if inp[k] is not None]
+    leaf_in = [k for k in names if k in want]                      # per-step inputs that get a gradient
+    leaf_w = [k for k in WKEYS if k in want]                       # resident parameters that get one (config 5)
 
-    def step(planes, pal, cam, focal, target):
-        rgb, depth, mask = render.render_planes(planes, pal, fld, H, W, cam, focal, None, None, S,
-                                                randomize=True, white_background=False, plane_dtype=pdt)
-        loss = (rgb - target).abs().mean() * B          # run.py:2236-2238 (l1)
-        grads = torch.autograd.grad(loss, [planes, pal, cam, focal])
-        return loss, rgb, depth, mask, grads
+    def make_step(check_hits, chunked):
+        def step(*tensors):
+            t = dict(zip(names, tensors))
+            for k in leaf_in:
+                t[k] = t[k].requires_grad_()
+            nb = t["cam"].shape[0]
+            rgb, depth, mask = render.render_planes(
+                t["planes"], t["palette"], fld, H, W, t["cam"], t.get("focal"), t.get("center"), None, S,
+                randomize=cfg["randomize"], white_background=cfg["white"], force_no_cam_grad=no_cam,
+                zbuffer_depth=cfg.get("zbuffer", False), check_hits=check_hits, plane_dtype=pdt)
+            if not backward:
+                return (rgb.sum() * 0, rgb, depth, mask)
+            diff = (rgb - t["target"]).abs()                       # run.py:2236-2238 (l1)
+            loss = diff.sum() * (1.0 / (H * W * 3)) if chunked else diff.mean() * nb
+            grads = torch.autograd.grad(loss, [t[k] for k in leaf_in] + [wdev[k] for k in leaf_w])
+            return (loss, rgb, depth, mask, *grads)
+        return step
 
     def barrier():
         if world > 1:
             dist.barrier()
         torch.cuda.synchronize()
 
+    # ---- config 5: the training step's gradient all-reduce (run.py:636-644, 980-986, 1064-1073) ------
+    ar_bufs, ar_ms = [], []
+    if cfg.get("allreduce") and world > 1:
+        ar_bufs = [torch.zeros(n, dtype=torch.float32, device=dev) for n in cfg["allreduce"]]
+
+    def allreduce_payloads(timed):
+        if not ar_bufs:
+            return
+        ev = (torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True))
+        ev[0].record()
+        for b in ar_bufs:
+            dist.all_reduce(b)
+        ev[1].record()
+        if timed:
+            ar_ms.append(ev)
+
     # ---- `value`: inputs resident in HBM ------------------------------------------------------
-    leaves = [t.to(dev).requires_grad_() for t in (planes_h, pal_h, cam_h, focal_h)]
-    target = target_h.to(dev)
+    step = make_step(True, False)
+    resident = [inp[k].to(dev) for k in names]
     torch.manual_seed(1234 + rank)
-    for _ in range(1 if args.e2e_only else args.warmup):
-        step(*leaves, target)
+    n_warm = 1 if args.e2e_only else args.warmup
+    for _ in range(n_warm):
+        step(*[t.detach() for t in resident])
+        allreduce_payloads(False)
     barrier()
     sampler = ClockSampler(local)
     if rank == 0:
@@ -144,8 +255,9 @@ def run_ours(args):
     barrier()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
-    for _ in range(1 if args.e2e_only else args.steps):
-        step(*leaves, target)
+    for _ in range(args.steps):
+        step(*[t.detach() for t in resident])
+        allreduce_payloads(True)
     e1.record()
     barrier()
     _lib.PROFILE.stop()
@@ -153,262 +265,225 @@ def run_ours(args):
     launches = _lib.PROFILE.launches
     durs = _lib.PROFILE.durations_ms()
     clocks = sampler.finish() if rank == 0 else None
+    ar_time = sum(a.elapsed_time(b) for a, b in ar_ms) / max(1, len(ar_ms))
+    del resident
 
     # ---- `e2e`: host buffers in, host buffers out, through the public API ---------------------
-    # the 1-GPU box has 4 GB of host memory: keep ONE host copy of the 403 MB planes (the pinned one)
+    # pinned host inputs -> (chunks of images over copy-in / compute / copy-out streams, chunk step replayed as a
+    # CUDA graph) -> pinned host outputs: loss, rgb, depth, mask and every gradient.  One pipeline, one code path,
+    # at every GPU count; a CUDA fault here fails the run (no retry, no fallback).
     pin = lambda t: t.contiguous().pin_memory()
-    planes_shape, pal_shape = tuple(planes_h.shape), tuple(pal_h.shape)
-    host_in = [pin(t) for t in (planes_h, pal_h, cam_h, focal_h, target_h)]
-    del planes_h, pal_h, cam_h, focal_h, target_h
+    host_in = [pin(inp[k]) for k in names]
+    shapes_out = [(), (B, H, W, 3), (B, H, W), (B, H, W)]
+    if backward:
+        shapes_out += [tuple(inp[k].shape) for k in leaf_in] + [tuple(fd[k].shape) for k in leaf_w]
+    inp = None
     import gc
     gc.collect()
-    host_out = [pin(torch.empty(s)) for s in ((), (B, H, W, 3), (B, H, W), (B, H, W), planes_shape,
-                                              pal_shape, (B, 4, 4), (B,))]
+    host_out = [pin(torch.empty(s)) for s in shapes_out]
     h2d = sum(t.numel() * 4 for t in host_in)
     d2h = sum(t.numel() * 4 for t in host_out)
-
-    # images are independent: chunks of images flow through copy-in / render+backward / copy-out on
-    # three streams (nfi_b200.host_pipeline), so PCIe traffic overlaps the kernels
-    from nfi_b200.host_pipeline import HostStepPipeline
-    if args.e2e_mode == "auto":
-        # multi-rank: at >= 4 GPUs the leg is bound by the box's host copy bandwidth either way,
-        # and a rank that faults cannot be re-measured -- see the known issue in DESIGN.md 5
-        args.e2e_mode = "graph" if world == 1 else "eager"
-    if args.e2e_chunks == "auto" and args.e2e_mode == "eager":
-        args.e2e_chunks = "8"                               # eager chunk steps are launch-bound below 2 images
     if args.e2e_chunks == "auto":
-        # short first / last chunks (their copy-in / copy-out overlaps nothing), 4-image chunks between
-        # (sweep on one B200, ms per step at B=16: 8x2 23.5 | 1,1,4,4,4,1,1 22.6 | 1,3,4,4,3,1 22.4)
-        if B >= 8:
-            mid, n_chunks = B - 2, [1]
-            while mid > 0:
-                n_chunks.append(min(4, mid) if mid not in (5, 6, 7) else 3)
-                mid -= n_chunks[-1]
-            left, right = [], []
-            for i, v in enumerate(sorted(n_chunks[1:])):        # smaller chunks towards the two ends
-                (left if i % 2 == 0 else right).append(v)
-            n_chunks = [1] + left + right[::-1] + [1]
-        else:
-            n_chunks = B
-    elif "," in args.e2e_chunks:                            # explicit chunk sizes (images)
-        n_chunks = [int(v) for v in args.e2e_chunks.split(",")]
-        if sum(n_chunks) != B:
-            n_chunks = 1
+        sizes = auto_chunks(B) if not leaf_w else [B]           # shared-parameter gradients: one chunk
     else:
-        n_chunks = int(args.e2e_chunks) if B % int(args.e2e_chunks) == 0 else 1
-
-    def chunk_step(p, a, c, f, tg):
-        p, a, c, f = [t.requires_grad_() for t in (p, a, c, f)]
-        rgb, depth, mask = render.render_planes(p, a, fld, H, W, c, f, None, None, S, randomize=True,
-                                                white_background=False, check_hits="defer", plane_dtype=pdt)
-        loss = (rgb - tg).abs().sum() * (1.0 / (H * W * 3))     # sums over chunks to .mean() * B
-        grads = torch.autograd.grad(loss, [p, a, c, f])
-        return (loss, rgb, depth, mask, *grads)
-
+        sizes = [int(v) for v in args.e2e_chunks.split(",")]
+        if len(sizes) == 1:
+            sizes = [B // sizes[0]] * sizes[0]
+        assert sum(sizes) == B, "--e2e-chunks does not partition the batch"
+    chunk_step = make_step("defer", True)
+    from nfi_b200.host_pipeline import GraphedHostStepPipeline, HostStepPipeline
+    if args.e2e_mode == "graph":
+        pipe = GraphedHostStepPipeline(chunk_step, B, sizes, dev, host_in, depth=args.e2e_depth)
+    else:
+        pipe = HostStepPipeline(chunk_step, B, sizes, dev)
     n_e2e = max(3, min(args.steps, 10))
-    e2e_note = None
-    e2e_stage = 0           # host-group barriers of the leg this rank has passed
-    e2e_failed = 0.0
-    try:
-        if args.e2e_mode == "graph":
-            from nfi_b200.host_pipeline import GraphedHostStepPipeline
-            pipe = GraphedHostStepPipeline(chunk_step, B, n_chunks, dev, host_in, depth=args.e2e_depth)
-        else:
-            pipe = HostStepPipeline(chunk_step, B, n_chunks, dev)
-        sizes = list(pipe.sizes)
-
-        def e2e_step():
-            pipe.run(host_in, host_out)                     # returns when the host results are complete
-            return float(host_out[0])
-
-        for _ in range(max(1, min(args.warmup, 3))):
-            e2e_step()
-        fake = os.environ.get("NFI_BENCH_FAKE_E2E_FAULT")            # test hook for the guard below
-        if fake and not args.e2e_only and (world == 1 or int(fake) == rank):
-            raise RuntimeError("injected end-to-end fault")
-        torch.cuda.synchronize()
-        if world > 1:
-            dist.barrier(group=host_group)
-        e2e_stage = 1
-        f0, f1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        f0.record()
-        for _ in range(n_e2e):
-            e2e_step()
-        f1.record()
-        torch.cuda.synchronize()
-        if world > 1:
-            dist.barrier(group=host_group)
-        e2e_stage = 2
-        e2e_ms = f0.elapsed_time(f1)
-    except Exception as exc:           # noqa: BLE001 -- a CUDA fault here must not cost the whole bench line
-        if args.e2e_only:
-            raise
-        if world > 1:
-            # keep the other ranks moving (they wait in the leg's host-group barriers), report the leg as
-            # unmeasured; the device-timed numbers of every rank are already on the host
-            sys.stderr.write("bench.py: rank %d: end-to-end leg failed (%s)\n" % (rank, exc))
-            for _ in range(2 - e2e_stage):
-                dist.barrier(group=host_group)
-            e2e_ms, sizes, e2e_failed = 0.0, [], 1.0
-            e2e_note = "unmeasured: the end-to-end leg faulted on a rank (%s)" % str(exc)[:120]
-        else:
-            # One such fault was seen in ~1500 end-to-end runs this round.  The device-timed
-            # numbers above are already on the host; the CUDA context of this process is gone, so the
-            # end-to-end leg is measured once more in a fresh process.
-            sys.stderr.write("bench.py: end-to-end leg failed (%s); re-measuring it in a fresh process\n" % exc)
-            host_in = host_out = pipe = leaves = target = None        # give the host and device memory back first
-            gc.collect()
-            try:
-                torch.cuda.empty_cache()
-            except Exception:                                          # noqa: BLE001 -- the context may be gone
-                pass
-            import subprocess
-            # the fresh process uses the eager pipeline (argparse: the last --e2e-mode / --e2e-chunks win)
-            sub = subprocess.run([sys.executable, os.path.abspath(__file__)] + sys.argv[1:] +
-                                 ["--e2e-only", "--e2e-mode", "eager", "--e2e-chunks", "8"],
-                                 capture_output=True, text=True, timeout=900)
-            line = [l for l in sub.stdout.strip().splitlines() if l.startswith("{")]
-            if sub.returncode == 0 and line:
-                got = json.loads(line[-1])
-                e2e_ms, n_e2e, sizes = got["e2e_ms"], got["n_e2e"], got["sizes"]
-                args.e2e_mode = "eager"
-                e2e_note = "re-measured in a fresh process (eager chunk steps) after a CUDA fault in the first attempt"
-            else:
-                sys.stderr.write("bench.py: the fresh process failed too (rc %d):\n%s\n" % (sub.returncode, sub.stderr[-3000:]))
-                e2e_ms, sizes = None, []
-                e2e_note = "unmeasured: the end-to-end leg faulted twice (%s)" % str(exc)[:120]
+    for _ in range(max(1, min(args.warmup, 3))):
+        pipe.run(host_in, host_out)
+        allreduce_payloads(False)
+    barrier()
+    f0, f1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    f0.record()
+    for _ in range(n_e2e):
+        pipe.run(host_in, host_out)                         # returns when the host results are complete
+        allreduce_payloads(False)
+        _ = float(host_out[0])
+    f1.record()
+    barrier()
+    e2e_ms = f0.elapsed_time(f1)
     if args.e2e_only:
         print(json.dumps({"e2e_ms": e2e_ms, "n_e2e": n_e2e, "sizes": sizes}))
         return
 
     # max over ranks
     if world > 1:
-        t = torch.tensor([ms_total, e2e_ms or 0.0, e2e_failed], dtype=torch.float64)
-        dist.all_reduce(t, op=dist.ReduceOp.MAX, group=host_group)
-        ms_total, e2e_ms = float(t[0]), float(t[1])
-        if float(t[2]) > 0:
-            e2e_ms = None
-            e2e_note = e2e_note or "unmeasured: the end-to-end leg faulted on another rank"
+        t = torch.tensor([ms_total, e2e_ms, ar_time], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms_total, e2e_ms, ar_time = float(t[0]), float(t[1]), float(t[2])
     if rank != 0:
-        if e2e_failed:            # broken CUDA context: skip NCCL teardown and destructors
-            os._exit(0)
-        if world > 1:
-            dist.destroy_process_group()
+        dist.destroy_process_group()
         return
+    report(args, cfg, world, B, B_total, H, W, ms_total, e2e_ms, n_e2e, sizes, h2d, d2h, launches, durs, clocks,
+           ar_time, dev)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def report(args, cfg, world, B, B_total, H, W, ms_total, e2e_ms, n_e2e, sizes, h2d, d2h, launches, durs, clocks,
+           ar_time, dev):
+    R = B * H * W
+    rays_job = (B_total if cfg["scaling"] == "strong" else B * world) * H * W
     ms_step = ms_total / args.steps
-    value = world * R / (ms_step * 1e-3)
-    e2e_value = world * R / (e2e_ms / n_e2e * 1e-3) if e2e_ms else None
+    value = rays_job / (ms_step * 1e-3)
+    e2e_value = rays_job / (e2e_ms / n_e2e * 1e-3)
     pk, pk_src = peaks()
-    # dominant kernel: field_bwd_ws_kernel (one launch = one 64-sample pass over every ray)
     samples = R * S
     bwd = durs.get("nfi_field_bwd", [])
     fwd = durs.get("nfi_field_fwd", [])
     bwd_ms = sum(bwd) / max(1, len(bwd))
     fwd_ms = sum(fwd) / max(1, len(fwd))
-    # algorithmic bytes of ONE field_bwd launch (DESIGN.md "field_bwd"): planes read once + plane
-    # gradient written once + per sample (upstream float4 16 + depth 4 + d/d point 12) + rays 24 B
-    a_bytes = 2 * B * PLANE_BYTES + samples * (16 + 4 + 12) + R * 24
-    ach = a_bytes / (bwd_ms * 1e-3) / 1e9 if bwd_ms > 0 else None
-    mlp_flops_bwd = samples * 5504              # backward-data only; the recompute is overhead
+    pose = "cam" in cfg["grads"]
+    if cfg["backward"]:
+        # dominant kernel: the field backward (one launch = one 64-sample pass over every ray).  Algorithmic bytes of
+        # ONE launch: planes read once + plane gradient written once + per sample (upstream float4 16
+        # + depth 4 [+ d/d point 12 with pose gradients]) + rays 24 B
+        kernel, k_ms, k_all = "field_bwd_ws_kernel" if "W0" not in cfg["grads"] else "field_bwd_tc_kernel<WANT_W>", bwd_ms, bwd
+        a_bytes = 2 * B * PLANE_BYTES + samples * (16 + 4 + (12 if pose else 0)) + R * 24
+    else:
+        # forward only: planes read once + per sample (depth 4 in, float4 16 out) + rays 24 B
+        kernel, k_ms, k_all = "field_fwd_ws_kernel", fwd_ms, fwd
+        a_bytes = B * PLANE_BYTES + samples * 20 + R * 24
+    ach = a_bytes / (k_ms * 1e-3) / 1e9 if k_ms > 0 else None
+    dtype = "f32" if args.plane_dtype == "f32" else "f32 (bf16 plane reads)"
     out = {
-        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
-        "warmup": args.warmup, "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak",
-        "vs_baseline": None, "dtype": "f32" if args.plane_dtype == "f32" else "f32 (bf16 plane reads)", "data": "synthetic",
-        "config": {"workload": "config2: inversion render fwd+bwd, B=%d images/GPU, %dx%d rays, 64+64 samples/ray, "
-                               "perspective, grads to planes/attention/cam/focal" % (B, H, W),
-                   "rays_per_step_per_gpu": R, "l2": "inputs (planes %d MB + gradients) exceed the 126 MB L2; no flush"
-                   % (B * PLANE_BYTES >> 20), "rng": "torch.rand uniforms drawn per step (parity mode)",
+        "metric": METRIC if cfg["backward"] else "rays/sec (fwd)", "value": value, "unit": UNIT, "n_gpus": world,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_step, "higher_is_better": True,
+        "scaling": cfg["scaling"], "vs_baseline": None, "dtype": dtype, "data": "synthetic",
+        "config": {"workload": "%s; B=%d images/GPU (%d over %d GPU%s), %dx%d rays, 64+64 samples/ray"
+                               % (cfg["label"], B, B_total, world, "" if world == 1 else "s", H, W),
+                   "id": args.config, "rays_per_step_per_gpu": R,
+                   "l2": ("inputs (planes %d MB + gradients) exceed the 126 MB L2; no flush" % (B * PLANE_BYTES >> 20))
+                   if B * PLANE_BYTES * (2 if cfg["backward"] else 1) > 126 << 20 else
+                   "inputs fit the 126 MB L2: a 256 MB buffer is not written between steps -- L2-warm number, stated",
+                   "rng": "torch.rand uniforms drawn per step (parity mode)" if cfg["randomize"] else "deterministic depths",
                    "e2e": "pinned host buffers; chunks of %s images pipelined over copy-in / compute / copy-out streams%s"
                    % ("+".join(str(v) for v in sizes),
                       ", chunk step replayed as a CUDA graph" if args.e2e_mode == "graph" else "")},
         "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
-                "steps": n_e2e, "ms_per_step": (e2e_ms / n_e2e) if e2e_ms else None,
-                **({"note": e2e_note} if e2e_note else {})},
+                "steps": n_e2e, "ms_per_step": e2e_ms / n_e2e},
         "gpu_launches": launches,
         "clocks": clocks,
-        "roofline": {"bound": "hbm", "kernel": "field_bwd_ws_kernel", "achieved": ach, "peak": pk["hbm_gbs"],
+        "roofline": {"bound": "hbm", "kernel": kernel, "achieved": ach, "peak": pk["hbm_gbs"],
                      "unit": "GB/s", "frac": (ach / pk["hbm_gbs"]) if ach else None,
-                     # dram__bytes_read.sum + dram__bytes_write.sum of one launch at this config, from the
-                     # committed ncu --set full capture (profiles/r01z_field_ws_ncu_full_summary.txt)
-                     "traffic": NCU_BWD_DRAM_BYTES if (B == 16 and H == 128) else None,
-                     "traffic_source": "profiles/r01z_field_ws_ncu_full_summary.txt",
+                     # dram__bytes_read.sum + dram__bytes_write.sum of one launch at config 2, from the committed
+                     # ncu --set full capture named in traffic_source
+                     "traffic": NCU_BWD_DRAM["bytes"] if (args.config == "2" and B == 16 and H == 128) else None,
+                     "traffic_source": NCU_BWD_DRAM["source"],
                      "peak_source": pk_src, "algorithmic_bytes_per_launch": a_bytes,
-                     "launch_ms": bwd_ms, "launches_timed": len(bwd),
-                     "share_of_step": (sum(bwd) / args.steps) / ms_step if ms_step else None,
-                     "mlp_tflops_bwd_data": mlp_flops_bwd / (bwd_ms * 1e-3) / 1e12 if bwd_ms > 0 else None,
+                     "launch_ms": k_ms, "launches_timed": len(k_all),
+                     "share_of_step": (sum(k_all) / args.steps) / ms_step if ms_step else None,
+                     "mlp_tflops_bwd_data": samples * 5504 / (bwd_ms * 1e-3) / 1e12 if bwd_ms > 0 else None,
                      # what ncu says actually limits this launch: not HBM, not the tensor pipe
-                     "measured_limiter": "instruction streams of the gather / MLP-chain roles (5.8 ms with all memory traffic "
-                                         "removed) plus the SM->L2 request path shared by 27 GB of L1-missing texel reads and "
-                                         "27.6 GB of red.v4.f32 lines (l1tex__m_l1tex2xbar_req_cycles_active 68%; the scatter "
-                                         "runs at 68% of the measured L2 reduction cap) -- DESIGN.md 4.2",
+                     "measured_limiter": "instruction streams and hand-offs of the gather / MLP-chain / scatter roles (5.8 ms "
+                                         "with all memory traffic removed); the plane-gradient reductions alone need 4.3 ms "
+                                         "at the measured L2 reduction cap (216 M red lines per launch at 49.6 G lines/s) "
+                                         "-- DESIGN.md 4.2",
                      "field_fwd_launch_ms": fwd_ms,
                      "field_fwd_share_of_step": (sum(fwd) / args.steps) / ms_step if ms_step else None},
     }
+    if cfg.get("allreduce"):
+        nbytes = sum(cfg["allreduce"]) * 4
+        out["allreduce"] = {"payload_bytes": nbytes, "ranks": world, "ms_per_step": ar_time if world > 1 else None,
+                            "bus_gbs": (2 * (world - 1) / world * nbytes / (ar_time * 1e-3) / 1e9)
+                            if (world > 1 and ar_time > 0) else None,
+                            "note": "two flat fp32 buffers (generator 32 164 056, discriminator 28 921 344 elements) "
+                                    "all-reduced with NCCL inside every timed step; single rank: no collective"}
     if not args.no_cpu_baseline and world == 1:
         try:                                  # reported baseline only: never fails the bench line
-            out["gpu_eager_baseline"] = gpu_eager_baseline(dev)
+            out["gpu_eager_baseline"] = gpu_eager_baseline(dev, cfg, B=min(B, args.eager_batch), res=H)
         except Exception as e:                # noqa: BLE001
             out["gpu_eager_baseline"] = {"unavailable": "%s: %s" % (type(e).__name__, str(e)[:200])}
-        out["cpu_baseline"] = cpu_baseline(sample_res=args.cpu_res)
+        torch.cuda.empty_cache()
+        out["cpu_baseline"] = cpu_baseline(cfg, sample_res=min(args.cpu_res, H))
     elif world > 1:
         out["cpu_baseline"] = None
     print(json.dumps(out))
-    if e2e_note:                  # the CUDA context of this process is broken: skip its destructors
-        sys.stdout.flush()
-        os._exit(0)
-    if world > 1:
-        dist.destroy_process_group()
 
 
 # ---------------------------------------------------------------------------------------------
-# CPU arm: the oracle port of the reference's PyTorch path (the reference itself is Python and
-# cannot travel to the GPU box; oracle/nfi_oracle.py is pinned to it by tests/golden/*).
+# Reference arms: the reference's OWN code for the path -- `render` lifted from run.py / eval_kitti_persp.py,
+# its `sampler` closure, `TriplanarDecoder.forward` and lib/nerf_utils.py, unmodified, from the files staged in
+# git-ignored oracle/_ref/ (oracle/build_ref.py; /root/reference in the build container) -- on the same synthetic
+# workload (the out-of-scope StyleGAN2 synthesis is replaced by a stub that returns the planes).  kind =
+# "reference".  Only when those files are absent does the oracle port (oracle/nfi_oracle.py) stand in (kind "port").
 # ---------------------------------------------------------------------------------------------
-def cpu_step_fn(B, res):
-    import nfi_oracle as O
+def reference_step_fn(cfg, B, res, device):
+    """-> (step() -> loss value, rays per step, kind)"""
+    import ref_loader
     H = W = res
-    S = 64
-    planes, fd, pal, cam, focal, target = make_inputs(B, H, W, S)
-    fp = O.FieldParams(fd["W0"], fd["b0"], fd["W1"], fd["b1"], SCENE_RANGE, True, 10, fd["beta"], fd["alpha"])
-    g = torch.Generator().manual_seed(1234)
+    inp = make_inputs(cfg, B, res=res)
+    fd = inp["field"]
+    want = cfg["grads"]
+    mv = lambda t: None if t is None else t.to(device)
+    base = {k: mv(inp[k]) for k in ("planes", "palette", "cam", "focal", "center", "target")}
+    no_cam = cfg["backward"] and "cam" not in want
+    train_w = any(k in want for k in WKEYS)
+    if ref_loader.available():
+        import ref_model
+        script = "eval_kitti_persp.py" if cfg.get("zbuffer") else "run.py"
+        render = ref_model.reference_render_fn(script, scene_range=cfg["scene_range"], white_background=cfg["white"])
+        G = ref_model.reference_generator(base["planes"], fd, cfg["scene_range"], trainable=train_w).to(device)
+        wparams = {"W0": G.decoder.net[0].weight, "b0": G.decoder.net[0].bias, "W1": G.decoder.net[2].weight,
+                   "b1": G.decoder.net[2].bias, "beta": G.beta, "alpha": G.alpha}
+        ws = torch.zeros(B, 15, 512, device=device)
+
+        def step():
+            lv = {k: base[k].clone().requires_grad_() for k in ("planes", "palette", "cam", "focal")
+                  if k in want and base[k] is not None}
+            t = {**base, **lv}
+            G.synthesis_network.planes = t["planes"]
+            out = render(G, H, W, t["cam"], t["focal"], t["center"], None, ws, S, randomize=cfg["randomize"],
+                         extra_model_inputs={"attention_values": t["palette"]}, force_no_cam_grad=no_cam)
+            if not cfg["backward"]:
+                return float(out[0].sum())
+            loss = (out[0] - t["target"]).abs().mean() * B
+            torch.autograd.grad(loss, list(lv.values()) + [wparams[k] for k in WKEYS if k in want])
+            return float(loss.detach())
+        return step, B * H * W, "reference"
+
+    import nfi_oracle as O
+    w = {k: fd[k].to(device).requires_grad_(k in want) for k in WKEYS}
+    fp = O.FieldParams(w["W0"], w["b0"], w["W1"], w["b1"], cfg["scene_range"], True, 10, w["beta"], w["alpha"])
+    gen = torch.Generator(device=device).manual_seed(1234)
 
     def step():
-        p = planes.clone().requires_grad_()
-        a = pal.clone().requires_grad_()
-        c = cam.clone().requires_grad_()
-        f = focal.clone().requires_grad_()
-        u_s = torch.rand(B, H, W, S, generator=g)
-        u_p = torch.rand(B * H * W, S, generator=g)
-        rgb, depth, mask = O.render(p.view(B, 3, 32, 256, 256), a, fp, H, W, c, f, None, None, S, False, u_s, u_p)
-        loss = (rgb - target).abs().mean() * B
-        torch.autograd.grad(loss, [p, a, c, f])
-        return float(loss)
+        lv = {k: base[k].clone().requires_grad_() for k in ("planes", "palette", "cam", "focal")
+              if k in want and base[k] is not None}
+        t = {**base, **lv}
+        u_s = torch.rand(B, H, W, S, generator=gen, device=device)
+        u_p = torch.rand(B * H * W, S, generator=gen, device=device)
+        rgb, depth, mask = O.render(t["planes"].view(B, 3, 32, 256, 256), t["palette"], fp, H, W, t["cam"], t["focal"],
+                                    t["center"], None, S, cfg["white"], u_s, u_p, cfg["randomize"], True, no_cam,
+                                    cfg.get("zbuffer", False))
+        if not cfg["backward"]:
+            return float(rgb.sum())
+        loss = (rgb - t["target"]).abs().mean() * B
+        torch.autograd.grad(loss, list(lv.values()) + [w[k] for k in WKEYS if k in want])
+        return float(loss.detach())
+    return step, B * H * W, "port"
 
-    return step, B * H * W
+
+def _what(kind):
+    return ("the reference's own PyTorch code (run.py::render, sampler closure, TriplanarDecoder, lib/nerf_utils.py; "
+            "oracle/_ref)" if kind == "reference" else "oracle port of the reference PyTorch path")
 
 
-def gpu_eager_baseline(dev, B=2, res=128, steps=3):
-    """The reference's eager PyTorch path ON THE SAME GPU ("the kernel to beat"): the
-    oracle port executes the reference's own ATen ops (grid_sample, linear, softplus, cumprod, sort,
-    gather ...), TF32 off as run.py:59-60 sets it.  Bounded sample: B images of config 2 per step."""
-    import nfi_oracle as O
+def gpu_eager_baseline(dev, cfg, B, res, steps=3):
+    """The reference's eager PyTorch path ON THE SAME GPU ("the kernel to beat"), TF32 off as
+    run.py:59-60 sets it, at the repo arm's batch when it fits (bounded by --eager-batch)."""
     torch.backends.cuda.matmul.allow_tf32 = False
     torch.backends.cudnn.allow_tf32 = False
-    H = W = res
-    S = 64
-    planes, fd, pal, cam, focal, target = [t.to(dev) if torch.is_tensor(t) else {k: v.to(dev) for k, v in t.items()}
-                                           for t in make_inputs(B, H, W, S)]
-    fp = O.FieldParams(fd["W0"], fd["b0"], fd["W1"], fd["b1"], SCENE_RANGE, True, 10, fd["beta"], fd["alpha"])
-
-    def step():
-        lv = [t.clone().requires_grad_() for t in (planes, pal, cam, focal)]
-        u_s = torch.rand(B, H, W, S, device=dev)
-        u_p = torch.rand(B * H * W, S, device=dev)
-        rgb, depth, mask = O.render(lv[0].view(B, 3, 32, 256, 256), lv[1], fp, H, W, lv[2], lv[3], None, None,
-                                    S, False, u_s, u_p)
-        loss = (rgb - target).abs().mean() * B
-        torch.autograd.grad(loss, lv)
-
+    torch.cuda.reset_peak_memory_stats(dev)
+    step, rays, kind = reference_step_fn(cfg, B, res, dev)
     step()
     torch.cuda.synchronize(dev)
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -419,52 +494,62 @@ def gpu_eager_baseline(dev, B=2, res=128, steps=3):
     torch.cuda.synchronize(dev)
     ms = e0.elapsed_time(e1) / steps
     peak_gb = torch.cuda.max_memory_allocated(dev) / 2**30
-    return {"value": B * H * W / (ms * 1e-3), "unit": UNIT, "kind": "port", "ms_per_step": ms,
-            "sample": "oracle port of the reference PyTorch path run eagerly on this GPU (TF32 off): %d images "
-                      "%dx%d rays (64+64 samples), fwd+bwd, %d timed steps after 1 warm-up; peak %.1f GiB allocated"
-                      % (B, res, res, steps, peak_gb)}
+    return {"value": rays / (ms * 1e-3), "unit": UNIT, "kind": kind, "ms_per_step": ms,
+            "sample": "%s run eagerly on this GPU (TF32 off): %d image(s) %dx%d rays (64+64 samples), %d timed steps after 1 "
+                      "warm-up; peak %.1f GiB allocated" % (_what(kind), B, res, res, steps, peak_gb)}
 
 
-def cpu_baseline(sample_res=64):
+def cpu_baseline(cfg, sample_res=128, budget_s=20.0):
+    """Bounded CPU sample on the box's host cores: B = 1 at sample_res x sample_res."""
     cores = os.cpu_count() or 1
     torch.set_num_threads(cores)
-    step, rays = cpu_step_fn(1, sample_res)
+    step, rays, kind = reference_step_fn(cfg, 1, sample_res, "cpu")
+    t0 = time.perf_counter()
     step()                                   # warm-up
+    warm = time.perf_counter() - t0
     n, t0 = 0, time.perf_counter()
     while True:
         step()
         n += 1
         dt = time.perf_counter() - t0
-        if dt > 12.0 or n >= 8:
+        if dt + warm > budget_s or n >= 8:
             break
-    return {"value": rays * n / dt, "unit": UNIT, "cores": cores, "kind": "port",
-            "sample": "oracle port of the reference PyTorch path, 1 image %dx%d rays (64+64 samples), fwd+bwd, "
-                      "%d timed steps after 1 warm-up, torch CPU with %d threads" % (sample_res, sample_res, n, cores)}
+    return {"value": rays * n / dt, "unit": UNIT, "cores": cores, "kind": kind,
+            "sample": "%s, 1 image %dx%d rays (64+64 samples) of this config, %d timed steps after 1 warm-up, torch CPU "
+                      "with %d threads" % (_what(kind), sample_res, sample_res, n, cores)}
 
 
 def run_reference(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
+    cfg = CONFIGS[args.config]
     cores = os.cpu_count() or 1
     torch.set_num_threads(cores)
-    res = args.cpu_res
-    step, rays = cpu_step_fn(1, res)
-    for _ in range(args.warmup):
+    res = min(args.cpu_res, args.res or cfg["res"])
+    step, rays, kind = reference_step_fn(cfg, 1, res, "cpu")
+    t0 = time.perf_counter()
+    step()
+    first = time.perf_counter() - t0
+    if first * (args.steps + args.warmup) > 300.0 and res > 64:      # keep the whole run within a few minutes
+        res = 64
+        step, rays, kind = reference_step_fn(cfg, 1, res, "cpu")
+    for _ in range(max(0, args.warmup - 1)):
         step()
     t0 = time.perf_counter()
     for _ in range(args.steps):
         step()
     dt = time.perf_counter() - t0
     value = rays * args.steps / dt
-    sample = ("each step = bounded sample of config 2: 1 image %dx%d rays (64+64 samples/ray), fwd+bwd, oracle "
-              "port of the reference PyTorch CPU path, %d torch threads" % (res, res, cores))
+    sample = ("each step = bounded sample of this config: 1 image %dx%d rays (64+64 samples/ray), %s, %d torch threads"
+              % (res, res, _what(kind), cores))
     print(json.dumps({
-        "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": int(os.environ.get("WORLD_SIZE", "1")),
+        "impl": "reference", "metric": METRIC if cfg["backward"] else "rays/sec (fwd)", "value": value, "unit": UNIT,
+        "n_gpus": int(os.environ.get("WORLD_SIZE", "1")),
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3,
-        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": "config2: inversion render fwd+bwd (CPU arm: " + sample + ")"},
-        "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
+        "higher_is_better": True, "scaling": cfg["scaling"], "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": cfg["label"] + " (CPU arm: " + sample + ")", "id": args.config},
+        "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": kind, "sample": sample},
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }))
 
@@ -475,19 +560,21 @@ def main():
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--batch", type=int, default=16, help="images per GPU (config 2: 16)")
-    ap.add_argument("--res", type=int, default=128)
-    ap.add_argument("--cpu-res", type=int, default=64, help="image size of the bounded CPU sample")
+    ap.add_argument("--config", default="2", choices=sorted(CONFIGS), help="BASELINE.json config (default 2)")
+    ap.add_argument("--batch", type=int, default=0, help="override the config's batch (images per GPU, or in total "
+                                                           "for the strong-scaling configs 3s / 3c)")
+    ap.add_argument("--res", type=int, default=0, help="override the config's image size")
+    ap.add_argument("--cpu-res", type=int, default=128, help="image size of the bounded CPU sample (BASELINE.md 4: 128)")
+    ap.add_argument("--eager-batch", type=int, default=16, help="largest batch of the eager-PyTorch-on-GPU baseline")
     ap.add_argument("--e2e-chunks", default="auto",
                     help="image chunks of the pipelined end-to-end leg: a count, or chunk sizes like 1,1,4,4,4,1,1")
-    ap.add_argument("--e2e-mode", choices=("auto", "graph", "eager"), default="auto",
-                    help="chunk step of the end-to-end leg: CUDA-graph replay or eager launches; auto = graph on "
-                         "one GPU (a fault there is re-measured in a fresh process), eager under torchrun")
+    ap.add_argument("--e2e-mode", choices=("graph", "eager"), default="graph",
+                    help="chunk step of the end-to-end leg: CUDA-graph replay (default, at every GPU count) or eager launches")
     ap.add_argument("--e2e-depth", type=int, default=2, help="graph instances used round-robin (graph mode)")
     ap.add_argument("--plane-dtype", choices=("f32", "bf16"), default="f32",
                     help="bf16: the gather reads a bfloat16 copy of the planes (the 1e-2 mode); default f32 (1e-4)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--e2e-only", action="store_true", help=argparse.SUPPRESS)   # internal: see run_ours
+    ap.add_argument("--e2e-only", action="store_true", help=argparse.SUPPRESS)   # developer switch
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else max(args.warmup, 1)
     if args.impl == "reference":

@@ -1,5 +1,6 @@
-"""bench.py's JSON line contract, on the arm that runs without a GPU: `--impl reference` (the CPU arm,
-oracle port of the reference path).  The GPU arm's line is produced on the box by the driver."""
+"""bench.py's JSON line contract, on the arm that runs without a GPU: `--impl reference` (the CPU arm: the
+reference's own render from oracle/_ref or /root/reference, else the oracle port).  The GPU arm's line is
+produced on the box by the driver."""
 import json
 import os
 import subprocess
@@ -27,10 +28,21 @@ def test_reference_arm_prints_one_contract_line():
     assert d["value"] > 0 and d["ms_per_step"] > 0 and d["vs_baseline"] is None and d["data"] == "synthetic"
     assert "workload" in d["config"] and "model" not in d["config"]
     cb = d["cpu_baseline"]
-    assert cb["kind"] == "port" and cb["cores"] >= 1 and cb["value"] == d["value"] and cb["sample"]
+    have_ref = os.path.exists("/root/reference/lib/nerf_utils.py") or \
+        os.path.exists(os.path.join(ROOT, "oracle", "_ref", "lib", "nerf_utils.py"))
+    assert cb["kind"] == ("reference" if have_ref else "port") and cb["cores"] >= 1 and cb["value"] == d["value"] and cb["sample"]
     assert d["e2e"] == {"value": d["value"], "unit": d["unit"], "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}
 
 
 def test_reference_arm_other_ranks_exit_quietly():
     """Under torchrun (N > 1) rank 0 alone runs and prints the CPU arm; the other ranks exit 0 without work."""
     assert _run("--gpus", "2", env={"RANK": "1", "WORLD_SIZE": "2", "LOCAL_RANK": "1"}) == []
+
+
+def test_every_config_runs_on_the_reference_arm():
+    for cid in ("1", "3s", "3c", "4", "5"):
+        lines = _run("--config", cid)
+        d = json.loads(lines[-1])
+        assert d["config"]["id"] == cid and d["value"] > 0
+        assert d["metric"] == ("rays/sec (fwd)" if cid == "1" else "rays/sec (fwd+bwd)")
+        assert d["scaling"] == ("strong" if cid.startswith("3") else "weak")
