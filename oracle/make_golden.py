@@ -220,6 +220,18 @@ def golden_render(only=()):
         "persp_n1": ("run.py", True, True, True, False, 1.4, 12, 12, False),
         "ortho_coords": ("run.py", False, True, False, False, 1.4, 12, 12, False),
     }
+    # round 2: rays in multiples of 8 x 16 so that the reference's own gradients pin the pixel-block tile
+    # schedule of the warp-specialised kernels (the cases above have H % 8 != 0 and take the linear tile order),
+    # on 64 x 64 / 32 x 32 planes (8 x 8 texel blocks), with the parameter sets of BASELINE.json config 3
+    cases.update({
+        "persp_tiles": ("run.py", True, True, False, False, 1.4, 16, 32, False),
+        # ShapeNet (data/loaders.py:120-123, 426-435): scene_range 0.55, white background, one focal, no pose gradient
+        "shapenet_tiles": ("run.py", True, True, True, True, 0.55, 16, 16, False),
+        # CUB (data/datasets.py:556-567): orthographic with T[3,3] != 1, scene_range 2.0
+        "cub_tiles": ("run.py", False, True, False, False, 2.0, 8, 16, False),
+    })
+    extra = {"persp_tiles": dict(B=1, res=64), "shapenet_tiles": dict(B=2, res=32, camera="shared_focal"),
+             "cub_tiles": dict(B=1, res=32, camera="cub")}
     n1 = {"persp_n1": dict(compute_normals=True, compute_semantics=True),
           "ortho_coords": dict(compute_coords=True)}
     for name, (script, persp, randomize, white, no_cam, sr, H, W, use_center) in cases.items():
@@ -228,6 +240,8 @@ def golden_render(only=()):
         B, S, res = 2, 64, 16
         if name == "kitti_zbuf":
             B = 1
+        ex = extra.get(name, {})
+        B, res = ex.get("B", B), ex.get("res", res)
         planes = synth.make_planes(B, res, seed=1).requires_grad_()
         field = synth.make_field(planes.detach(), seed=3)
         palette = synth.make_palette(B, 10, seed=4).requires_grad_()
@@ -235,9 +249,15 @@ def golden_render(only=()):
             cam, _ = synth.make_cameras(B, seed=2, focal_range=(2.0, 2.0), dist_jitter=(2.2, 2.2))
             focal = torch.tensor(3.1)                       # 0-dim, eval_kitti_persp.py:948
             center = torch.tensor([[0.56, 0.47]])
+        elif ex.get("camera") == "cub":
+            cam, focal, center = synth.make_ortho_cub_cameras(B, seed=7), None, None
         else:
             cam, focal = synth.make_cameras(B, seed=2, perspective=persp)
             center = None
+            if ex.get("camera") == "shared_focal":
+                cam = cam.clone()
+                cam[:, :3, 3] *= sr / 1.4
+                focal = focal[:1].expand(B).contiguous()
         cam = cam.detach().requires_grad_()
         if focal is not None:
             focal = focal.detach().requires_grad_()

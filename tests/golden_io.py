@@ -41,6 +41,6 @@ def render_case(name):
     return g
 
 
-RENDER_CASES = ["persp_rand", "ortho_det", "persp_white_nocam", "kitti_zbuf"]
+RENDER_CASES = ["persp_rand", "ortho_det", "persp_white_nocam", "kitti_zbuf", "persp_tiles", "shapenet_tiles", "cub_tiles"]
 # forward-only fixtures of the extra render outputs; g["flags"] = (normals, semantics, coords)
 N1_CASES = ["persp_n1", "ortho_coords"]
