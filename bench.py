@@ -143,6 +143,38 @@ def make_inputs(cfg, B, seed_shift=0, res=None):
     return dict(planes=planes, palette=pal, cam=cam, focal=focal, center=center, target=target, field=fd)
 
 
+def bind_to_gpu_numa_node(index):
+    """Multi-rank runs: pin this process to the cores of the NUMA node its GPU hangs off, BEFORE the pinned host
+    buffers are allocated (first touch then places them on that node).  torchrun starts every rank on the same
+    cores by default; with 8 ranks copying 0.8 GB per step each way, host memory on the wrong socket halves the
+    copy bandwidth per GPU (profiles/r01w_pcie_probe_8gpus_concurrent.txt).  Returns the node or None."""
+    try:
+        bdf = torch.cuda.get_device_properties(index).pci_bus_id if hasattr(torch.cuda.get_device_properties(index), "pci_bus_id") else None
+        if bdf is None:
+            q = subprocess.run(["nvidia-smi", "-i", str(index), "--query-gpu=pci.bus_id", "--format=csv,noheader"],
+                               capture_output=True, text=True, timeout=20).stdout.strip()
+            bdf = q
+        bdf = bdf.lower()
+        if len(bdf.split(":")[0]) == 8:                  # nvidia-smi prints an 8-digit PCI domain, sysfs uses 4
+            bdf = bdf[4:]
+        with open("/sys/bus/pci/devices/%s/numa_node" % bdf) as f:
+            node = int(f.read().strip())
+        if node < 0:
+            return None
+        with open("/sys/devices/system/node/node%d/cpulist" % node) as f:
+            cpus = set()
+            for part in f.read().strip().split(","):
+                a, _, b = part.partition("-")
+                cpus.update(range(int(a), int(b or a) + 1))
+        allowed = os.sched_getaffinity(0) & cpus
+        if allowed:
+            os.sched_setaffinity(0, allowed)
+            return node
+    except Exception:
+        pass
+    return None
+
+
 def auto_chunks(B):
     """Image chunks of the pipelined end-to-end leg: short first / last chunks (their copy-in / copy-out overlaps
     nothing), 4-image chunks between (sweep on one B200, ms per step at B=16: 8x2 23.5 | 1,1,4,4,4,1,1 22.6 |
@@ -172,6 +204,7 @@ def run_ours(args):
     local = int(os.environ.get("LOCAL_RANK", "0"))
     assert torch.cuda.is_available(), "bench.py (impl=ours) needs a CUDA device; there is no CPU fallback"
     torch.cuda.set_device(local)
+    numa = bind_to_gpu_numa_node(local) if world > 1 and not args.no_numa_bind else None
     dev = torch.device("cuda", local)
     if world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
@@ -323,13 +356,13 @@ def run_ours(args):
         dist.destroy_process_group()
         return
     report(args, cfg, world, B, B_total, H, W, ms_total, e2e_ms, n_e2e, sizes, h2d, d2h, launches, durs, clocks,
-           ar_time, dev)
+           ar_time, dev, numa)
     if world > 1:
         dist.destroy_process_group()
 
 
 def report(args, cfg, world, B, B_total, H, W, ms_total, e2e_ms, n_e2e, sizes, h2d, d2h, launches, durs, clocks,
-           ar_time, dev):
+           ar_time, dev, numa=None):
     R = B * H * W
     rays_job = (B_total if cfg["scaling"] == "strong" else B * world) * H * W
     ms_step = ms_total / args.steps
@@ -369,7 +402,8 @@ def report(args, cfg, world, B, B_total, H, W, ms_total, e2e_ms, n_e2e, sizes, h
                    % ("+".join(str(v) for v in sizes),
                       ", chunk step replayed as a CUDA graph" if args.e2e_mode == "graph" else "")},
         "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
-                "steps": n_e2e, "ms_per_step": e2e_ms / n_e2e},
+                "steps": n_e2e, "ms_per_step": e2e_ms / n_e2e,
+                **({"numa_node_rank0": numa} if numa is not None else {})},
         "gpu_launches": launches,
         "clocks": clocks,
         "roofline": {"bound": "hbm", "kernel": kernel, "achieved": ach, "peak": pk["hbm_gbs"],
@@ -574,6 +608,7 @@ def main():
     ap.add_argument("--plane-dtype", choices=("f32", "bf16"), default="f32",
                     help="bf16: the gather reads a bfloat16 copy of the planes (the 1e-2 mode); default f32 (1e-4)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-numa-bind", action="store_true", help="multi-rank runs: do not pin the rank to its GPU's NUMA node")
     ap.add_argument("--e2e-only", action="store_true", help=argparse.SUPPRESS)   # developer switch
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else max(args.warmup, 1)
