@@ -118,7 +118,6 @@ struct BwSmem {
   uint64_t meta_full[kBwNM], meta_empty[kBwNM];
   uint32_t tmem_base;
   uint32_t pad;
-  Args args;                             // the launch arguments (read by the role functions)
 };
 
 __device__ __forceinline__ int bw_any(const BwMeta& m) {
@@ -161,7 +160,7 @@ __device__ __forceinline__ void bw_prefetch(const Args& a, BwIn& in, int b, int 
 
 // phase 1 of one sample: activity from the upstream gradient, texel offsets, fractions
 template <bool PTS, int MODE>
-__device__ __forceinline__ bool bw_phase1_16(const Args& a, BwTable& tb, const BwIn& in, int b, int t,
+__device__ __forceinline__ bool bw_phase1(const Args& a, BwTable& tb, const BwIn& in, int b, int t,
                                           int row, int li, int per_image) {
   int ray;
   const int sid = sample_and_ray(a, t, row, ray);
@@ -213,79 +212,6 @@ __device__ __forceinline__ bool bw_phase1_16(const Args& a, BwTable& tb, const B
   }
   tb.keep[row] = keep;
   tb.sid[row] = sid;
-  return act;
-}
-
-// phase 1 of one sample: activity from the upstream gradient, texel offsets, fractions
-template <bool PTS, int MODE>
-__device__ __forceinline__ bool bw_phase1(const Args& a, BwTable& tb, const BwIn& in, int b, int t,
-                                          int row, int li, int half, int per_image) {
-  int ray;
-  const int sid = sample_and_ray(a, t, row, ray);
-  float keep = -1.f;
-  bool act = false;
-  float ma = 0.f, mb = 0.f, ta = 0.f, tbv = 0.f;
-  uint32_t c0 = 0, c1 = 0, r0 = 0, r1 = 0;
-  if (sid >= 0) {
-    const int64_t id = (int64_t)b * per_image + sid;
-    float pt[3];
-    if (PTS) { pt[0] = in.o[li][0]; pt[1] = in.o[li][1]; pt[2] = in.o[li][2]; }
-    else {
-      const float o[3] = {in.o[li][0], in.o[li][1], in.o[li][2]};
-      const float d[3] = {in.d[li][0], in.d[li][1], in.d[li][2]};
-      nfi_point(o, d, in.o[li][3], pt);
-    }
-    float x[3];
-#pragma unroll
-    for (int i = 0; i < 3; ++i) x[i] = NFI_DIV(pt[i], a.f.scene_range);
-    keep = 1.f;
-    if (MODE == 0 && (fabsf(x[0]) > 1.f || fabsf(x[1]) > 1.f || fabsf(x[2]) > 1.f)) keep = 0.f;
-    if (MODE == 0) {
-      const float4 g = in.g[li];
-      const bool col = (g.y != 0.f) || (g.z != 0.f) || (g.w != 0.f);
-      // outside the box sigma is masked (generator.py:634): only a colour gradient can act;
-      // samples with an all-zero upstream gradient are skipped exactly
-      act = col || (g.x != 0.f && keep > 0.5f);
-    } else {
-#pragma unroll
-      for (int o = 0; o < NFI_YPAD; ++o) if (o < a.f.n_out) act = act || (a.g_out[id * a.f.n_out + o] != 0.f);
-    }
-    if (!act) keep = -2.f;
-    if (act) {
-      // One axis footprint = (first texel index, second one clamped in bounds, fraction, d i / d x).  The three
-      // planes need four of them -- x as a column (planes xy, xz), y as a row (xy) and as a column (yz), z as a
-      // row (xz, yz) -- not six.  The two lanes of a row split them: half 0 takes x-column and y-row and
-      // assembles planes xy and xz, half 1 takes y-column and z-row and assembles plane yz; the z-row goes
-      // from half 1 to half 0 by shuffle (done below, outside this branch: all lanes take part).
-      const float xa = half == 0 ? x[0] : x[1];          // axis used as a column by this half
-      const float xb = half == 0 ? x[1] : x[2];          // axis used as a row
-      const float fa = nfi_unnormalize(xa, a.Wp, &ma), fb = nfi_unnormalize(xb, a.Hp, &mb);
-      const float fla = floorf(fa), flb = floorf(fb);
-      const int a0 = (int)fla, b0 = (int)flb;
-      const int a1 = a0 + 1 < a.Wp ? a0 + 1 : a.Wp - 1, b1 = b0 + 1 < a.Hp ? b0 + 1 : a.Hp - 1;
-      ta = NFI_SUB(fa, fla); tbv = NFI_SUB(fb, flb);
-      c0 = (uint32_t)nfi_texel_col(a0, a.bshift); c1 = (uint32_t)nfi_texel_col(a1, a.bshift);
-      r0 = (uint32_t)nfi_texel_row(b0, a.bshift, a.nbx); r1 = (uint32_t)nfi_texel_row(b1, a.bshift, a.nbx);
-    }
-  }
-  // z-row of half 1 -> half 0 (lanes l and l ^ 16 hold the same row)
-  const uint32_t zr0 = __shfl_xor_sync(0xffffffffu, r0, 16), zr1 = __shfl_xor_sync(0xffffffffu, r1, 16);
-  const float zt = __shfl_xor_sync(0xffffffffu, tbv, 16), zm = __shfl_xor_sync(0xffffffffu, mb, 16);
-  if (act) {
-    const uint32_t pt_ = (uint32_t)(a.Hp * a.Wp);
-    // ATen zeroes out-of-range neighbours (within_bounds_2d) in the coordinate gradient; that only happens at
-    // ix == Wp-1 (iy == Hp-1), where the clamp already makes the multiplier zero
-    const int p = half == 0 ? 0 : 2;           // xy (x-col, y-row) | yz (y-col, z-row)
-    const uint32_t q0 = p * pt_ + r0, q1 = p * pt_ + r1;
-    tb.toff[p][row] = make_uint4((q0 + c0) * 128u, (q0 + c1) * 128u, (q1 + c0) * 128u, (q1 + c1) * 128u);
-    tb.tder[p][row] = make_float4(ta, tbv, ma, mb);
-    if (half == 0) {                           // xz: x-col (mine), z-row (from half 1)
-      const uint32_t s0 = pt_ + zr0, s1 = pt_ + zr1;
-      tb.toff[1][row] = make_uint4((s0 + c0) * 128u, (s0 + c1) * 128u, (s1 + c0) * 128u, (s1 + c1) * 128u);
-      tb.tder[1][row] = make_float4(ta, zt, ma, zm);
-    }
-  }
-  if (half == 0) { tb.keep[row] = keep; tb.sid[row] = sid; }
   return act;
 }
 
@@ -450,13 +376,39 @@ __device__ long long g_bw_trace[kBtRoles * kBtN * kBtEv];
 #endif
 
 template <bool PTS, int MODE, bool WANT_PTS, bool BF16>
-__device__ __noinline__ void bw_role_gather(const Args& a, BwSmem& sm, const uint32_t tmem, const int warp, const int lane) {
+__global__ void __launch_bounds__(kBwThreads, 1)
+field_bwd_ws_kernel(const Args a) {
+  extern __shared__ __align__(128) unsigned char smem_raw[];
+  BwSmem& sm = *reinterpret_cast<BwSmem*>(smem_raw);
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  nfi_mlp::load_weights(sm.w, a.f.W0, a.f.b0, a.f.W1, a.f.b1, a.f.n_out);
+  nfi_mlp::load_weights_bwd(sm.bw, a.f.W0, a.f.W1, a.f.n_out);
+  if (tid == 0) {
+    for (int c = 0; c < 2; ++c) {
+      nfi_tc::mbar_init(&sm.a_full[c], kBwPS);  if (c < kBwNA) nfi_tc::mbar_init(&sm.a_empty[c], 1);
+      nfi_tc::mbar_init(&sm.df_full[c], 1);     nfi_tc::mbar_init(&sm.s_free[c], kBwS);
+    }
+    nfi_tc::mbar_init(&sm.acc_full, 1);
+    nfi_tc::mbar_init(&sm.acc_ready, kBwE);
+    for (int i = 0; i < kBwNM; ++i) {
+      nfi_tc::mbar_init(&sm.meta_full[i], kBwPS);
+      nfi_tc::mbar_init(&sm.meta_empty[i], kBwE + kBwS + 1);
+    }
+    nfi_tc::mbar_fence_init();
+  }
+  constexpr int kMmaWarp = kBwPS + kBwE + kBwS;
+  if (warp == kMmaWarp) nfi_tc::tmem_alloc(&sm.tmem_base, kBwTmemCols);
+  nfi_tc::fence_proxy_async();
+  nfi_tc::fence_before_sync();
+  __syncthreads();
+  nfi_tc::fence_after_sync();
+  const uint32_t tmem = sm.tmem_base;
   const int per_image = (int)(a.npi * a.S);
   const TileMap tm = cta_tile_map(a.tiles_per_image);
   const int ntile = tm.ntile;
   const uint32_t total = (uint32_t)a.B * (uint32_t)ntile;
-  constexpr int kMmaWarp = kBwPS + kBwE + kBwS;
-  (void)per_image; (void)kMmaWarp; (void)total;
+
+  if (warp < kBwPS) {
     // ------------------------------------------------------------------ gather
     const int w = warp, q = w & 3, half = w >> 2;
     const int row = bw_row(w, lane & (kBwRows - 1));
@@ -474,11 +426,7 @@ __device__ __noinline__ void bw_role_gather(const Args& a, BwSmem& sm, const uin
       if (w == 0 && lane == 0) NFI_BTRACE(0, it, 0);
       bool act = false;
       cp_async_wait_all();
-#ifdef NFI_BW_PH1_16
-      if (lane < kBwRows) act = bw_phase1_16<PTS, MODE>(a, tb, in, b, t, row, lane, per_image);
-#else
-      act = bw_phase1<PTS, MODE>(a, tb, in, b, t, row, lane & (kBwRows - 1), lane >> 4, per_image);   // 2 lanes per row
-#endif
+      if (lane < kBwRows) act = bw_phase1<PTS, MODE>(a, tb, in, b, t, row, lane, per_image);
       const unsigned wany = __any_sync(0xffffffffu, act);
       if (lane == 0) sm.meta[m].flag[w] = wany ? 1 : 0;
       __syncwarp();
@@ -514,16 +462,7 @@ __device__ __noinline__ void bw_role_gather(const Args& a, BwSmem& sm, const uin
       if (lane == 0) nfi_tc::mbar_arrive(&sm.a_full[c]);
       if (w == 0 && lane == 0) NFI_BTRACE(0, it, 3);
     }
-}
-
-template <bool PTS, int MODE, bool WANT_PTS, bool BF16>
-__device__ __noinline__ void bw_role_epilogue(const Args& a, BwSmem& sm, const uint32_t tmem, const int warp, const int lane) {
-  const int per_image = (int)(a.npi * a.S);
-  const TileMap tm = cta_tile_map(a.tiles_per_image);
-  const int ntile = tm.ntile;
-  const uint32_t total = (uint32_t)a.B * (uint32_t)ntile;
-  constexpr int kMmaWarp = kBwPS + kBwE + kBwS;
-  (void)per_image; (void)kMmaWarp; (void)total;
+  } else if (warp < kBwPS + kBwE) {
     // ------------------------------------------------------------------ epilogue: the MLP chain
     const int ew = warp - kBwPS;
     const int row = ew * 32 + lane;
@@ -646,16 +585,7 @@ __device__ __noinline__ void bw_role_epilogue(const Args& a, BwSmem& sm, const u
       if (lane == 0) nfi_tc::mbar_arrive(&sm.meta_empty[m]);
     }
     flush();
-}
-
-template <bool PTS, int MODE, bool WANT_PTS, bool BF16>
-__device__ __noinline__ void bw_role_scatter(const Args& a, BwSmem& sm, const uint32_t tmem, const int warp, const int lane) {
-  const int per_image = (int)(a.npi * a.S);
-  const TileMap tm = cta_tile_map(a.tiles_per_image);
-  const int ntile = tm.ntile;
-  const uint32_t total = (uint32_t)a.B * (uint32_t)ntile;
-  constexpr int kMmaWarp = kBwPS + kBwE + kBwS;
-  (void)per_image; (void)kMmaWarp; (void)total;
+  } else if (warp < kMmaWarp) {
     // ------------------------------------------------------------------ scatter: dF (+ T) -> gradients
     const int sw = warp - kBwPS - kBwE;
     const int row = sw * 32 + lane;
@@ -733,16 +663,7 @@ __device__ __noinline__ void bw_role_scatter(const Args& a, BwSmem& sm, const ui
       __syncwarp();
       if (lane == 0) nfi_tc::mbar_arrive(&sm.meta_empty[m]);
     }
-}
-
-template <bool PTS, int MODE, bool WANT_PTS, bool BF16>
-__device__ __noinline__ void bw_role_mma(const Args& a, BwSmem& sm, const uint32_t tmem, const int warp, const int lane) {
-  const int per_image = (int)(a.npi * a.S);
-  const TileMap tm = cta_tile_map(a.tiles_per_image);
-  const int ntile = tm.ntile;
-  const uint32_t total = (uint32_t)a.B * (uint32_t)ntile;
-  constexpr int kMmaWarp = kBwPS + kBwE + kBwS;
-  (void)per_image; (void)kMmaWarp; (void)total;
+  } else {
     // ------------------------------------------------------------------ MMA issuer
     // the whole warp waits (converged); one elected lane issues the MMAs, commits and arrives
     uint32_t rph = 0;
@@ -784,45 +705,6 @@ __device__ __noinline__ void bw_role_mma(const Args& a, BwSmem& sm, const uint32
       if (lane == 0) NFI_BTRACE(4, it, 3);
     }
   }
-
-template <bool PTS, int MODE, bool WANT_PTS, bool BF16>
-__global__ void __launch_bounds__(kBwThreads, 1)
-field_bwd_ws_kernel(const Args a_param) {
-  extern __shared__ __align__(128) unsigned char smem_raw[];
-  BwSmem& sm = *reinterpret_cast<BwSmem*>(smem_raw);
-  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-  // Every role runs in its own __noinline__ function: ptxas then allocates registers per role instead of over
-  // the whole kernel (one role's live ranges and spills no longer perturb the others -- round-2 A/B, DESIGN.md
-  // 4.2), and the launch arguments are read from this shared-memory copy
-  if (tid == 0) sm.args = a_param;
-  nfi_mlp::load_weights(sm.w, a_param.f.W0, a_param.f.b0, a_param.f.W1, a_param.f.b1, a_param.f.n_out);
-  nfi_mlp::load_weights_bwd(sm.bw, a_param.f.W0, a_param.f.W1, a_param.f.n_out);
-  if (tid == 0) {
-    for (int c = 0; c < 2; ++c) {
-      nfi_tc::mbar_init(&sm.a_full[c], kBwPS);  if (c < kBwNA) nfi_tc::mbar_init(&sm.a_empty[c], 1);
-      nfi_tc::mbar_init(&sm.df_full[c], 1);     nfi_tc::mbar_init(&sm.s_free[c], kBwS);
-    }
-    nfi_tc::mbar_init(&sm.acc_full, 1);
-    nfi_tc::mbar_init(&sm.acc_ready, kBwE);
-    for (int i = 0; i < kBwNM; ++i) {
-      nfi_tc::mbar_init(&sm.meta_full[i], kBwPS);
-      nfi_tc::mbar_init(&sm.meta_empty[i], kBwE + kBwS + 1);
-    }
-    nfi_tc::mbar_fence_init();
-  }
-  constexpr int kMmaWarp = kBwPS + kBwE + kBwS;
-  if (warp == kMmaWarp) nfi_tc::tmem_alloc(&sm.tmem_base, kBwTmemCols);
-  nfi_tc::fence_proxy_async();
-  nfi_tc::fence_before_sync();
-  __syncthreads();
-  nfi_tc::fence_after_sync();
-  const uint32_t tmem = sm.tmem_base;
-  const Args& a = sm.args;
-
-  if (warp < kBwPS) bw_role_gather<PTS, MODE, WANT_PTS, BF16>(a, sm, tmem, warp, lane);
-  else if (warp < kBwPS + kBwE) bw_role_epilogue<PTS, MODE, WANT_PTS, BF16>(a, sm, tmem, warp, lane);
-  else if (warp < kMmaWarp) bw_role_scatter<PTS, MODE, WANT_PTS, BF16>(a, sm, tmem, warp, lane);
-  else bw_role_mma<PTS, MODE, WANT_PTS, BF16>(a, sm, tmem, warp, lane);
   nfi_tc::fence_before_sync();
   __syncthreads();
   if (warp == kMmaWarp) nfi_tc::tmem_dealloc(tmem, kBwTmemCols);
