@@ -283,7 +283,7 @@ def run_ours(args):
     if rank == 0:
         sampler.start()
         time.sleep(0.3)
-    timed = ("nfi_field_fwd", "nfi_field_bwd")
+    timed = ("nfi_field_fwd", "nfi_field_bwd", "nfi_field_bwd_train")
     _lib.PROFILE.start(timed)
     barrier()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -370,7 +370,7 @@ def report(args, cfg, world, B, B_total, H, W, ms_total, e2e_ms, n_e2e, sizes, h
     e2e_value = rays_job / (e2e_ms / n_e2e * 1e-3)
     pk, pk_src = peaks()
     samples = R * S
-    bwd = durs.get("nfi_field_bwd", [])
+    bwd = durs.get("nfi_field_bwd", []) + durs.get("nfi_field_bwd_train", [])
     fwd = durs.get("nfi_field_fwd", [])
     bwd_ms = sum(bwd) / max(1, len(bwd))
     fwd_ms = sum(fwd) / max(1, len(fwd))
@@ -379,8 +379,12 @@ def report(args, cfg, world, B, B_total, H, W, ms_total, e2e_ms, n_e2e, sizes, h
         # dominant kernel: the field backward (one launch = one 64-sample pass over every ray).  Algorithmic bytes of
         # ONE launch: planes read once + plane gradient written once + per sample (upstream float4 16
         # + depth 4 [+ d/d point 12 with pose gradients]) + rays 24 B
-        kernel, k_ms, k_all = "field_bwd_ws_kernel" if "W0" not in cfg["grads"] else "field_bwd_tc_kernel<WANT_W>", bwd_ms, bwd
+        train = "W0" in cfg["grads"]
+        kernel, k_ms, k_all = ("field_bwd_ws_kernel" if not train else
+                               "field_bwd_ws_kernel<STASH> + wgrad_reduce_kernel (one nfi_field_bwd_train call)"), bwd_ms, bwd
         a_bytes = 2 * B * PLANE_BYTES + samples * (16 + 4 + (12 if pose else 0)) + R * 24
+        if train:      # + the per-sample rows F, H, dHpre, dY (704 B) written by the backward and read by the reduction
+            a_bytes += samples * 2 * 705
     else:
         # forward only: planes read once + per sample (depth 4 in, float4 16 out) + rays 24 B
         kernel, k_ms, k_all = "field_fwd_ws_kernel", fwd_ms, fwd

@@ -141,6 +141,19 @@ int nfi_field_bwd(const NfiField* field, const float* planes_cl, const float* pa
                   const float* g_out, float* g_planes_cl, float* g_palette, float* g_points,
                   float* g_params, int want_weight_grads, nfi_stream_t stream);
 
+/* Generator-training gradient set (run.py:980-986, models/stylegan.py:170-177): nfi_field_bwd for ray samples in heads
+ * mode (points == NULL, mode 0) with want_weight_grads = 1, on the warp-specialised kernel: the backward leaves F, H,
+ * dHpre, dY of every sample in `workspace` (704 bytes per sample + 1) and one reduction kernel forms dW0, db0, dW1, db1
+ * from them.  g_params as in nfi_field_bwd (accumulating, caller zero-fills; ALL of W0,b0,W1,b1,beta,alpha are
+ * written).  workspace: 256-byte aligned, >= nfi_field_bwd_train_workspace_bytes(B * n_per_image * S); callers bound
+ * it by splitting the batch by image (gradients accumulate). */
+size_t nfi_field_bwd_train_workspace_bytes(int64_t n_samples);
+int nfi_field_bwd_train(const NfiField* field, const float* planes_cl, const float* palette, int B, int Hp,
+                        int Wp, const float* origins, const float* dirs, const float* z, int64_t n_per_image,
+                        int S, int img_w, const float* g_out, float* g_planes_cl, float* g_palette,
+                        float* g_points, float* g_params, void* workspace, size_t workspace_bytes,
+                        nfi_stream_t stream);
+
 /* ---- decoder MLP alone (models/generator.py:295-299, 329-330; EqualizedLinear gains applied
  *      inside): feat [n,32] -> y [n, n_out] on tcgen05 tensor cores (3xTF32 split, fp32
  *      accumulate in TMEM).  hpre [n,64] (optional) receives the hidden pre-activations. --------- */

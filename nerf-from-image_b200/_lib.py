@@ -61,6 +61,9 @@ _SIGS = {
                               c_int, c_int, c_int, c_int, _P, _P, _P]),
     "nfi_field_bwd": (c_int, [POINTER(NfiField), _P, _P, c_int, c_int, c_int, _P, _P, _P, _P, c_int64,
                               c_int, c_int, c_int, _P, _P, _P, _P, _P, c_int, _P]),
+    "nfi_field_bwd_train_workspace_bytes": (ctypes.c_size_t, [c_int64]),
+    "nfi_field_bwd_train": (c_int, [POINTER(NfiField), _P, _P, c_int, c_int, c_int, _P, _P, _P, c_int64, c_int, c_int,
+                                    _P, _P, _P, _P, _P, _P, ctypes.c_size_t, _P]),
     "nfi_decoder_mlp_fwd": (c_int, [POINTER(NfiField), _P, c_int64, _P, _P, _P]),
     "nfi_weights_only": (c_int, [_P, c_int, _P, _P, c_int64, c_int, c_int, _P, _P]),
     "nfi_sample_pdf": (c_int, [_P, _P, c_int64, c_int, c_int, _P, _P, _P, _P]),
@@ -120,7 +123,7 @@ def stream_of(t):
 
 
 # kernels launched per C-ABI call (everything else launches exactly one)
-KERNELS_PER_CALL = {"nfi_near_far": 2, "nfi_near_far_static": 2}
+KERNELS_PER_CALL = {"nfi_near_far": 2, "nfi_near_far_static": 2, "nfi_field_bwd_train": 2}
 
 
 class LaunchProfile:

@@ -250,9 +250,9 @@ __device__ __forceinline__ float4 bw_weights(const float4& d) {
 // scalar, 7.24 / 7.47 -- both need more live registers, and at the 96-register cap of this 17-warp CTA
 // ptxas then spills inside this loop (320 instead of 144 bytes of spill loads).  The packed form is kept
 // where registers allow it: the scatter below and the forward gather (126 registers).
-template <bool WANT_PTS, bool BF16>
+template <bool WANT_PTS, bool BF16, bool STASH>
 __device__ __forceinline__ void bw_gather(const Args& a, const BwTable& tb, float* a_hi, float* a_lo, float* tq,
-                                          int b, int w, int lane) {
+                                          int b, int w, int lane, float* st_f) {
   const int c4 = lane & 7;
   const float third = 1.f / 3.f;
   const char* base = reinterpret_cast<const char*>(a.planes) +
@@ -294,6 +294,8 @@ __device__ __forceinline__ void bw_gather(const Args& a, const BwTable& tb, floa
       }
     }
     nfi_mlp::store_feat4(a_hi, a_lo, s, c4, acc);
+    // training path: the feature row stays in the caller's workspace for the weight-gradient reduction
+    if (STASH && tb.keep[s] >= 0.f) *reinterpret_cast<float4*>(st_f + (int64_t)tb.sid[s] * 32 + c4 * 4) = acc;
   }
 }
 
@@ -375,7 +377,7 @@ __device__ long long g_bw_trace[kBtRoles * kBtN * kBtEv];
 #define NFI_BTRACE(role, it, ev) do {} while (0)
 #endif
 
-template <bool PTS, int MODE, bool WANT_PTS, bool BF16>
+template <bool PTS, int MODE, bool WANT_PTS, bool BF16, bool STASH = false>
 __global__ void __launch_bounds__(kBwThreads, 1)
 field_bwd_ws_kernel(const Args a) {
   extern __shared__ __align__(128) unsigned char smem_raw[];
@@ -449,7 +451,8 @@ field_bwd_ws_kernel(const Args a) {
       if (it >= 2) nfi_tc::mbar_wait(&sm.s_free[c], ((it >> 1) - 1) & 1);
       if (bw_any(sm.meta[m])) {
         if (w == 0 && lane == 0) NFI_BTRACE(0, it, 2);
-        bw_gather<WANT_PTS, BF16>(a, tb, sm.a[ca][0], sm.a[ca][1], sm.tq[q], b, w, lane);
+        bw_gather<WANT_PTS, BF16, STASH>(a, tb, sm.a[ca][0], sm.a[ca][1], sm.tq[q], b, w, lane,
+                                         STASH ? a.st_f + (int64_t)b * per_image * 32 : nullptr);
         if (WANT_PTS) {
           nfi_tc::named_bar_sync(1 + q, 64);             // both halves of the quarter are in the scratch
           bw_store_t(sm.tq[q], tmem + lane_off + kBwColT + 96 * c, half, lane);
@@ -491,6 +494,7 @@ field_bwd_ws_kernel(const Args a) {
       const BwTable& tb = sm.tab[it % kBwNT];
       const int sid = tb.sid[row];
       const float keep = tb.keep[row];
+      if (STASH && sid >= 0) a.st_ok[(int64_t)b * per_image + sid] = (keep >= 0.f) ? 1 : 0;   // idle tiles too
       if (bw_any(sm.meta[m])) {
         if (b != cur_b) {
           flush();
@@ -519,7 +523,8 @@ field_bwd_ws_kernel(const Args a) {
         nfi_tc::mbar_wait(&sm.acc_full, ph); ph ^= 1;
         if (ew == 0 && lane == 0) NFI_BTRACE(2, it, 0);
         nfi_tc::fence_after_sync();
-        nfi_mlp::epilogue0_at<4>(sm.w.b0, tl, 0);
+        if (STASH) nfi_mlp::epilogue0_at_keep<4>(sm.w.b0, tl, 0, act ? a.st_h + id * 64 : nullptr);
+        else nfi_mlp::epilogue0_at<4>(sm.w.b0, tl, 0);
         nfi_tc::fence_before_sync();
         __syncwarp();
         if (lane == 0) nfi_tc::mbar_arrive(&sm.acc_ready);
@@ -551,6 +556,11 @@ field_bwd_ws_kernel(const Args a) {
           for (int o = 0; o < NFI_YPAD; ++o) dy[o] = gy[o];
         }
         nfi_mlp::store_dy(tl, dy);
+        if (STASH && act) {
+#pragma unroll
+          for (int i = 0; i < 4; ++i)
+            *reinterpret_cast<float4*>(a.st_dy + id * 16 + 4 * i) = make_float4(dy[4 * i], dy[4 * i + 1], dy[4 * i + 2], dy[4 * i + 3]);
+        }
         nfi_tc::fence_before_sync();
         __syncwarp();
         if (lane == 0) nfi_tc::mbar_arrive(&sm.acc_ready);
@@ -575,7 +585,8 @@ field_bwd_ws_kernel(const Args a) {
         nfi_tc::mbar_wait(&sm.acc_full, ph); ph ^= 1;
         if (ew == 0 && lane == 0) NFI_BTRACE(3, it, 0);
         nfi_tc::fence_after_sync();
-        nfi_mlp::epilogue2<4>(tl, 0);
+        if (STASH) nfi_mlp::epilogue2_keep<4>(tl, 0, act ? a.st_dh + id * 64 : nullptr);
+        else nfi_mlp::epilogue2<4>(tl, 0);
         nfi_tc::fence_before_sync();
         __syncwarp();
         if (lane == 0) nfi_tc::mbar_arrive(&sm.acc_ready);

@@ -43,6 +43,9 @@ struct Args {
   // backward
   const float* g_out;
   float* g_planes; float* g_palette; float* g_points; float* g_params;
+  // generator-training path (nfi_field_bwd_train): per-sample rows the backward leaves in a caller workspace for the
+  // weight-gradient reduction -- F [n,32], H [n,64], dHpre [n,64], dY [n,16], and a validity byte per sample
+  float* st_f; float* st_h; float* st_dh; float* st_dy; unsigned char* st_ok;
 };
 
 // One 16-byte feature chunk (4 channels) of a texel.  `off` is the texel's byte offset in the fp32 layout

@@ -45,6 +45,7 @@ static inline int fill_args(Args& a, const char* who, const NfiField* field, con
   a.inv_bx = a.blocks_x > 0 ? 1.f / (float)a.blocks_x : 1.f;
   a.out = nullptr; a.probs = nullptr; a.g_out = nullptr;
   a.g_planes = a.g_palette = a.g_points = a.g_params = nullptr;
+  a.st_f = a.st_h = a.st_dh = a.st_dy = nullptr; a.st_ok = nullptr;
   return NFI_OK;
 }
 

@@ -236,6 +236,31 @@ __device__ __forceinline__ void epilogue0_at(const float* __restrict__ b0, uint3
   }
   nfi_tc::tmem_st_wait();
 }
+// same, and the row of H (64 floats, 16-byte aligned) is also written to `hrow` when it is not NULL
+template <int NQ>
+__device__ __forceinline__ void epilogue0_at_keep(const float* __restrict__ b0, uint32_t tl, int col0, float* hrow) {
+#pragma unroll
+  for (int q = 0; q < NQ; ++q) {
+    float v[16];
+    nfi_tc::tmem_ld16(tl + kColD0 + col0 + 16 * q, v);
+    nfi_tc::tmem_ld_wait();
+    uint32_t hi[16], lo[16];
+#pragma unroll
+    for (int i = 0; i < 16; ++i) {
+      v[i] = softplus_f(v[i] + b0[col0 + 16 * q + i]);
+      hi[i] = nfi_tc::tf32_hi(v[i]);
+      lo[i] = __float_as_uint(v[i] - __uint_as_float(hi[i]));
+    }
+    nfi_tc::tmem_st16(tl + kColHhi + col0 + 16 * q, hi);
+    nfi_tc::tmem_st16(tl + kColHlo + col0 + 16 * q, lo);
+    if (hrow) {
+#pragma unroll
+      for (int i = 0; i < 4; ++i)
+        *reinterpret_cast<float4*>(hrow + col0 + 16 * q + 4 * i) = make_float4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
+    }
+  }
+  nfi_tc::tmem_st_wait();
+}
 __device__ __forceinline__ void epilogue1_at(const float* __restrict__ b1, uint32_t tl, float (&y)[16]) {
   nfi_tc::tmem_ld16(tl + kColD1, y);
   nfi_tc::tmem_ld_wait();
@@ -344,6 +369,35 @@ __device__ __forceinline__ void epilogue2(uint32_t tmem_lane, int col0) {
     }
     nfi_tc::tmem_st16(tmem_lane + kColHhi + col0 + 16 * q, hi);
     nfi_tc::tmem_st16(tmem_lane + kColHlo + col0 + 16 * q, lo);
+  }
+  nfi_tc::tmem_st_wait();
+}
+
+// same, and the row of dHpre is also written to `drow` when it is not NULL
+template <int NQ>
+__device__ __forceinline__ void epilogue2_keep(uint32_t tmem_lane, int col0, float* drow) {
+#pragma unroll
+  for (int q = 0; q < NQ; ++q) {
+    float dh[16], hh[16], hl[16];
+    nfi_tc::tmem_ld16(tmem_lane + kColDH + col0 + 16 * q, dh);
+    nfi_tc::tmem_ld16(tmem_lane + kColHhi + col0 + 16 * q, hh);
+    nfi_tc::tmem_ld16(tmem_lane + kColHlo + col0 + 16 * q, hl);
+    nfi_tc::tmem_ld_wait();
+    uint32_t hi[16], lo[16];
+#pragma unroll
+    for (int i = 0; i < 16; ++i) {
+      const float sg = 1.f - nfi_tc::ex2_ftz((hh[i] + hl[i]) * -1.4426950408889634f);
+      dh[i] = dh[i] * sg;
+      hi[i] = nfi_tc::tf32_hi(dh[i]);
+      lo[i] = __float_as_uint(dh[i] - __uint_as_float(hi[i]));
+    }
+    nfi_tc::tmem_st16(tmem_lane + kColHhi + col0 + 16 * q, hi);
+    nfi_tc::tmem_st16(tmem_lane + kColHlo + col0 + 16 * q, lo);
+    if (drow) {
+#pragma unroll
+      for (int i = 0; i < 4; ++i)
+        *reinterpret_cast<float4*>(drow + col0 + 16 * q + 4 * i) = make_float4(dh[4 * i], dh[4 * i + 1], dh[4 * i + 2], dh[4 * i + 3]);
+    }
   }
   nfi_tc::tmem_st_wait();
 }

@@ -324,9 +324,13 @@ class _Field(Function):
         want_params = want_w or (cfg.use_sdf and mode == 0 and (need[6] or need[7]))
         g_params = torch.zeros(sum(_param_sizes(n_out)), dtype=torch.float32, device=pl.device) \
             if want_params else None
-        call("nfi_field_bwd", pl, field, ptr(src), ptr(pal), B, Hp, Wp, ptr(o), ptr(d), ptr(zz), ptr(pts),
-             ctx.npi, ctx.S, mode, ctx.img_w, ptr(g), ptr(g_planes), ptr(g_pal), ptr(g_points),
-             ptr(g_params), int(want_w))
+        if want_w and pts is None and mode == 0 and ctx.planes_bf16 is None:
+            _field_bwd_train(field, pl, pal, B, Hp, Wp, o, d, zz, ctx.npi, ctx.S, ctx.img_w, g, g_planes, g_pal,
+                             g_points, g_params)
+        else:
+            call("nfi_field_bwd", pl, field, ptr(src), ptr(pal), B, Hp, Wp, ptr(o), ptr(d), ptr(zz), ptr(pts),
+                 ctx.npi, ctx.S, mode, ctx.img_w, ptr(g), ptr(g_planes), ptr(g_pal), ptr(g_points),
+                 ptr(g_params), int(want_w))
         go = gd = gp = None
         if want_pts:
             if pts is None:
@@ -351,6 +355,30 @@ class _Field(Function):
                 gb1 = g_params[o2:base].view_as(b1) if need[5] else None
         return (ret_planes, g_pal, gW0, gb0, gW1, gb1, g_beta, g_alpha, go, gd, None, gp,
                 None, None, None, None, None, None, None)
+
+
+TRAIN_WORKSPACE_CAP = 6 << 30     # bytes; larger batches go image chunk by image chunk (gradients accumulate)
+
+
+def _field_bwd_train(field, pl, pal, B, Hp, Wp, o, d, zz, npi, S, img_w, g, g_planes, g_pal, g_points, g_params):
+    """Generator-training gradient set (run.py:980-986) through nfi_field_bwd_train: the warp-specialised backward
+    plus one weight-gradient reduction kernel.  The workspace (705 bytes per sample) is bounded by splitting
+    the batch by image; every output slice of an image chunk is contiguous."""
+    l = _lib.lib()
+    per_img = int(l.nfi_field_bwd_train_workspace_bytes(npi * S))
+    nb = max(1, min(B, TRAIN_WORKSPACE_CAP // max(per_img, 1)))
+    ws_bytes = int(l.nfi_field_bwd_train_workspace_bytes(nb * npi * S))
+    ws = torch.empty(ws_bytes, dtype=torch.uint8, device=pl.device)
+    o2, d2 = o.reshape(B, npi, 3), d.reshape(B, npi, 3)
+    z2, g2 = zz.reshape(B, npi, S), g.reshape(B, npi, S, 4)
+    gp2 = None if g_points is None else g_points.view(B, npi, S, 3)
+    for b0 in range(0, B, nb):
+        b1 = min(B, b0 + nb)
+        sl = slice(b0, b1)
+        call("nfi_field_bwd_train", pl, field, ptr(pl[sl]), None if pal is None else ptr(pal[sl]), b1 - b0, Hp, Wp,
+             ptr(o2[sl]), ptr(d2[sl]), ptr(z2[sl]), npi, S, img_w, ptr(g2[sl]),
+             None if g_planes is None else ptr(g_planes[sl]), None if g_pal is None else ptr(g_pal[sl]),
+             None if gp2 is None else ptr(gp2[sl]), ptr(g_params), ptr(ws), ws_bytes)
 
 
 def decoder_mlp(feat, W0, b0, W1, b1, want_hidden=False):
