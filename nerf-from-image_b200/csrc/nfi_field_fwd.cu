@@ -159,3 +159,17 @@ extern "C" int nfi_field_fwd(const NfiField* field, const float* planes_cl, cons
     return NFI_OK;
   }
 }
+
+#ifdef NFI_WAIT_FLAG
+// Developer reproducer builds only (see nfi_field_bwd.cu): timed-out bounded waits of THIS translation unit.
+extern "C" int nfi_debug_wait_timeouts_fwd(int reset) {
+  int v = -1;
+  if (cudaDeviceSynchronize() != cudaSuccess) return -2;
+  if (cudaMemcpyFromSymbol(&v, nfi_tc::g_nfi_wait_timeouts, sizeof(int)) != cudaSuccess) return -3;
+  if (reset) {
+    const int zero = 0;
+    if (cudaMemcpyToSymbol(nfi_tc::g_nfi_wait_timeouts, &zero, sizeof(int)) != cudaSuccess) return -4;
+  }
+  return v;
+}
+#endif

@@ -321,6 +321,14 @@ field_fwd_ws_kernel(const Args a) {
           pend.valid = true; pend.it = it; pend.c = c; pend.cph = cph; pend.m = m; pend.id = id; pend.keep = keep; pend.b = b;
           ++act;
         } else {
+          // An idle tile must not leave the previous active tile pending: its meta slot is only released by
+          // finish(), and a producer that wraps the ring of kNM meta slots (an active tile followed by >= kNM - 1
+          // idle ones: a pixel block that hits the box followed by blocks that miss it) would wait for that
+          // release while this warp waits for the producer's next meta_full -- the deadlock behind the launch
+          // failures of BASELINE config 3 (round 2; tests/test_ws_protocol.py::test_forward_idle_run_after_active_tile)
+#ifndef NFI_FWD_OLD_DEFER       // developer reproducer of the round-1 behaviour
+          if (pend.valid) finish();
+#endif
           if (ew < 4 && MODE == 0 && id >= 0) {             // whole tile outside the box
             reinterpret_cast<float4*>(a.out)[id] = make_float4(0.f, 0.f, 0.f, 0.f);
             if (a.probs) for (int q = 0; q < hd.A; ++q) a.probs[id * hd.A + q] = 0.f;
@@ -349,6 +357,18 @@ field_fwd_ws_kernel(const Args a) {
         if (lane == 0) NFI_TRACE(3, it, 0);
         if (!any) {
           if (nfi_tc::elect_one()) nfi_tc::mbar_arrive(&sm.a_empty[s]);
+#ifndef NFI_FWD_OLD_DEFER
+          if (pend) {                                       // layer 1 of the last active tile: do not defer it past idle tiles
+            nfi_tc::mbar_wait(&sm.h_full[pc], pph);
+            nfi_tc::fence_after_sync();
+            if (nfi_tc::elect_one()) {
+              nfi_mlp::issue_layer1_at(sm.w, tmem + pc * kAccCols);
+              nfi_tc::mma_commit(&sm.d1_full[pc]);
+            }
+            __syncwarp();
+            pend = false;
+          }
+#endif
           continue;
         }
         nfi_tc::fence_after_sync();

@@ -94,3 +94,68 @@ def test_injected_scatter_delay_is_harmless_with_the_shipped_protocol():
 def test_injected_scatter_delay_deadlocks_the_round1_protocol():
     """The round-1 wait discipline, same delay: waits run out of spins (the launch failure of round 1)."""
     assert _run("oldproto_delay", reps=3) > 0
+
+
+_FWD_DRIVER = r'''
+import ctypes, sys, torch
+sys.path.insert(0, %(root)r)
+from nfi_b200 import _lib, decoder, render, synth
+lib = _lib.lib()
+dbg = getattr(lib, "nfi_debug_wait_timeouts_fwd", None)
+if dbg is not None:
+    dbg.restype = ctypes.c_int; dbg.argtypes = [ctypes.c_int]
+B, H, W, S, res = 3, 16, 32, 64, 32
+planes = synth.make_planes(B, res=res, seed=1).cuda().requires_grad_()
+fd = synth.make_field(planes.detach().cpu(), seed=3)
+fld = decoder.Field(*[fd[k].cuda() for k in ("W0", "b0", "W1", "b1", "beta", "alpha")], 0.55, 10, True)
+pal = synth.make_palette(B, 10, seed=4).cuda().requires_grad_()
+cam, focal = synth.make_cameras(B, seed=2, perspective=True)
+cam = cam.clone()
+cam[:, :3, 3] *= 0.55 / 1.4
+cam[1:, :3, 3] += 50.0 * cam[1:, :3, 0]     # images 1, 2: camera moved far along its own x axis -> every ray misses
+cam = cam.cuda().requires_grad_(); focal = focal.cuda().requires_grad_()
+worst = 0
+for rep in range(3):
+    if dbg is None:
+        rgb, depth, mask = render.render_planes(planes, pal, fld, H, W, cam, focal, None, None, S, randomize=True,
+                                                white_background=True)
+        torch.autograd.grad((rgb - 0.3).abs().mean() + mask.mean(), [planes, pal, cam, focal])
+        torch.cuda.synchronize()
+    else:                      # flag-raising builds: forward only (a drained launch leaves garbage behind)
+        with torch.no_grad():
+            rgb, depth, mask = render.render_planes(planes, pal, fld, H, W, cam, focal, None, None, S, randomize=True,
+                                                    white_background=True)
+        worst = max(worst, dbg(1))
+if worst == 0:
+    assert float(mask[0].mean()) > 0.02, "image 0 must see the box"
+    assert float(mask[1:].abs().max()) == 0.0 and float((rgb[1:] - 1.0).abs().max()) == 0.0
+print("TIMEOUTS", worst)
+'''
+
+
+def _run_fwd(libname):
+    env = dict(os.environ)
+    if libname:
+        path = os.path.join(LIBDIR, "libnfi_b200_%s.so" % libname)
+        if not os.path.exists(path):
+            pytest.skip("%s not built (python tools/build_protocol_variants.py)" % path)
+        env["NFI_B200_LIB"] = path
+    r = subprocess.run([sys.executable, "-c", _FWD_DRIVER % {"root": ROOT}], env=env, capture_output=True, text=True,
+                       timeout=600)
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-4000:]
+    return int(r.stdout.strip().splitlines()[-1].split()[1])
+
+
+def test_forward_idle_run_after_active_tile():
+    """Round-2 finding (BASELINE config 3 under torchrun): the forward kernel deferred the heads of an active tile
+    until the NEXT active tile; an active tile followed by a run of >= 7 idle tiles (a pixel block that hits the
+    scene box followed by blocks that miss it -- here: image 0 sees the box, images 1 and 2 look away from it)
+    wrapped the ring of 8 meta slots and deadlocked producer and epilogue (bounded wait -> launch failure).
+    Fixed by finishing the pending tile on idle tiles (nfi_field_fwd_ws.cuh)."""
+    assert _run_fwd(None) == 0                  # shipped library: forward + backward, results checked
+    assert _run_fwd("fwd_flag") == 0            # same kernel with flag-raising waits: none runs out of spins
+
+
+def test_forward_idle_run_deadlocks_the_round1_deferral():
+    """The round-1 behaviour (-DNFI_FWD_OLD_DEFER), same inputs: bounded waits run out of spins."""
+    assert _run_fwd("fwd_old_defer") > 0

@@ -10,23 +10,27 @@ sys.path.insert(0, os.path.join(HERE, "..", "nerf-from-image_b200"))
 import build as B  # noqa: E402
 
 COMMON = ["-DNFI_WAIT_FLAG", "-DNFI_WAIT_SPINS=(1u<<18)", "-DNFI_BW_INJECT_SCATTER_DELAY=60"]
-VARIANTS = {"newproto_delay": COMMON, "oldproto_delay": COMMON + ["-DNFI_BW_OLD_PROTOCOL"]}
-SRC = "nfi_field_bwd.cu"
+VARIANTS = {"newproto_delay": ("nfi_field_bwd.cu", COMMON),
+            "oldproto_delay": ("nfi_field_bwd.cu", COMMON + ["-DNFI_BW_OLD_PROTOCOL"]),
+            # forward kernel: the round-1 deferral of a tile's heads to the next ACTIVE tile (deadlocks on idle runs)
+            "fwd_old_defer": ("nfi_field_fwd.cu", ["-DNFI_WAIT_FLAG", "-DNFI_WAIT_SPINS=(1u<<18)", "-DNFI_FWD_OLD_DEFER"]),
+            "fwd_flag": ("nfi_field_fwd.cu", ["-DNFI_WAIT_FLAG", "-DNFI_WAIT_SPINS=(1u<<18)"])}
 
 
 def build(force=False):
     B.build()
-    src = os.path.join(B.CSRC, SRC)
-    deps = [src] + [os.path.join(B.CSRC, f) for f in os.listdir(B.CSRC) if f.endswith(".cuh")]
+    hdrs = [os.path.join(B.CSRC, f) for f in os.listdir(B.CSRC) if f.endswith(".cuh")]
     procs = []
-    for name, flags in VARIANTS.items():
+    for name, (SRC, flags) in VARIANTS.items():
+        src = os.path.join(B.CSRC, SRC)
+        deps = [src] + hdrs
         lib = os.path.join(B.LIBDIR, "libnfi_b200_%s.so" % name)
         if not force and not B._stale(lib, deps + [os.path.abspath(__file__)]):
             continue
         o = os.path.join(B.LIBDIR, "proto_%s.o" % name)
         cmd = [B._nvcc()] + B.NVCC_FLAGS + flags + ["-c", src, "-o", o]
-        procs.append((name, o, lib, subprocess.Popen(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT)))
-    for name, o, lib, p in procs:
+        procs.append((name, SRC, o, lib, subprocess.Popen(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT)))
+    for name, SRC, o, lib, p in procs:
         out = p.communicate()[0].decode()
         if p.returncode:
             raise RuntimeError("nvcc failed for %s:\n%s" % (name, out))
