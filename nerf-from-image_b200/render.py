@@ -122,6 +122,79 @@ def render_planes(planes, palette, field: Field, height: int, width: int, tform_
     return rgb, depth, mask
 
 
+def render_viewdir(model_for, height, width, tform_cam2world, focal_length=None,
+                   center=None, bbox=None, depth_samples_per_ray: int = 64, randomize: bool = True,
+                   white_background: bool = False, fine_sampling: bool = True, force_no_cam_grad: bool = False,
+                   zbuffer_depth: bool = False, check_hits=True, scene_range: float = 1.0):
+    """the view-direction branch (CARLA; models/generator.py:189-253, 468-469, 662-663).
+
+    With `use_viewdir` the decoder has 1 + 32 outputs and the 32 features of a sample are modulated by a per-ray
+    vector before the colour head: y = LeakyReLU(x_ray + features) -> EqualizedLinear(32 -> A or 3).  This path is a
+    HYBRID, not the fused kernels: rays, depths, importance sampling, merge and compositing are the library's
+    kernels; the triplane gather + decoder MLP run on the tensor-core kernel in raw-decoder mode, three passes of 11
+    of the 33 outputs each (the kernels hold at most 16 outputs); the per-ray modulation, the output layer and the
+    density / colour heads (generator.py:629-636, 661-679) are PyTorch ops on [B, N, 33] tensors.  Functionally
+    complete with autograd to planes, decoder, mapper, palette and pose; about 4x the fused path's time.
+    `model_for(viewdirs)` is called ONCE, after the rays exist (the generator needs the view directions before it
+    can build its sampler, generator.py:468-469), with `viewdirs` [B,H,W,1,3]; it returns (gen, planes [B,96,Hp,Wp],
+    palette [B,A,3] or None, mapper_closure) -- `gen` supplies decoder / beta / alpha / scene_range /
+    attention_values / use_sdf, `mapper_closure` is the reference's (generator.py:241-251).  `scene_range` must be
+    given because the near/far planes are needed before the generator runs."""
+    import torch.nn.functional as F
+    H, W, S = int(height), int(width), int(depth_samples_per_ray)
+    cam = tform_cam2world
+    B = cam.shape[0]
+    dev = cam.device
+    sr = float(scene_range)
+    o, d = ops.ray_bundle(H, W, focal_length, cam, bbox, center, normalize=True)
+    near, far = ops.near_far(o, d, sr, check_hits=check_hits)
+    u = torch.rand((B, H, W, S), dtype=torch.float32, device=dev) if randomize else None
+    z_c = ops.stratified(near, far, S, randomize, u)
+    o_s, d_s = (o.detach(), d.detach()) if force_no_cam_grad else (o, d)
+    gen, planes, palette, closure = model_for(d_s.unsqueeze(-2))
+    assert abs(float(gen.scene_range) - sr) < 1e-12
+    planes_cl = ops.planes_to_channels_last(planes)
+    l0, l2 = gen.decoder.net[0], gen.decoder.net[2]
+    n_out = l2.weight.shape[0]
+    assert n_out == 33, "use_viewdir decoders have 1 + 32 outputs (models/generator.py:375-376)"
+    cfg11 = ops.FieldConfig(attention_values=10, use_sdf=False, scene_range=1.0)
+    A = int(gen.attention_values)
+
+    def field(z):
+        pts = ops.points_on_rays(o_s, d_s, z)                                   # [B,H,W,S,3]
+        x = (pts / sr).reshape(B, -1, 3)
+        with torch.no_grad():
+            oob = (x.abs() > 1).any(dim=-1).float()                             # generator.py:605-607
+        ys = [ops.field_on_points(planes_cl, None, l0.weight, l0.bias, l2.weight[k:k + 11], l2.bias[k:k + 11], None,
+                                  None, x, cfg11, mode=1)[0] for k in (0, 11, 22)]
+        y = torch.cat(ys, dim=-1)                                               # [B,N,33]
+        dist, feat = y[..., 0], y[..., 1:].contiguous()
+        if gen.use_sdf:                                                         # generator.py:629-636
+            nd = -dist
+            cdf = 0.5 + 0.5 * torch.sign(nd) * (1 - torch.exp(-nd.abs() / gen.beta))
+            sigma = (1 / gen.alpha) * (cdf * (1 - oob))
+        else:                                                                   # generator.py:637-641
+            sigma = F.softplus(dist - 1) * (1 - oob)
+        feat = closure(feat)                                                    # generator.py:662-663
+        if A == 0:
+            rgb = torch.sigmoid(feat) * 2.004 - 1.002                           # generator.py:36-39, 665-666
+        else:
+            rgb = torch.matmul(F.softmax(feat, dim=-1), palette)                # generator.py:668-678
+        return torch.cat((sigma.unsqueeze(-1), rgb), dim=-1).view(B, H, W, S, 4).contiguous()
+
+    coarse = field(z_c)
+    if not fine_sampling:
+        rgb, depth, mask, _, _ = ops.composite(coarse[..., 0], coarse[..., 1:], d.detach(), z_c, None, None,
+                                               white_background)
+        return rgb, depth, mask
+    u_pdf = torch.rand((B * H * W, S), dtype=torch.float32, device=dev) if randomize else None
+    z_f = ops.importance(coarse.detach(), d, z_c, u_pdf, sigma_stride=4)
+    fine = field(z_f)
+    rgb, depth, mask, _, _ = ops.merge_composite(coarse, fine, z_c, z_f, d, white_background,
+                                                 cam.detach() if zbuffer_depth else None)
+    return rgb, depth, mask
+
+
 def _closure_vars(fn):
     """Free variables of the reference's `sampler` closure (models/generator.py:587).  Cells that the
     generator never assigned stay out of the result: `viewdir_mapper_closure` only exists with
@@ -140,12 +213,34 @@ def make_render(args, dataset_config, zbuffer_depth: bool = False):
     `args` (use_viewdir, use_sdf, attention_values, fine_sampling) and `dataset_config`
     (scene_range, white_background) globals that the reference function reads (run.py:200-348)."""
 
+    def _render_with_viewdir(target_model, height, width, cam, focal, center, bbox, model_input, S, randomize,
+                             extra_model_outputs, extra_model_inputs, force_no_cam_grad):
+        box = {}
+
+        def model_for(viewdirs):
+            outs = target_model(viewdirs, model_input, ["sampler"] + list(extra_model_outputs), extra_model_inputs)
+            cv = _closure_vars(outs.pop("sampler"))
+            box["outs"] = outs
+            gen = cv["self"]
+            palette = cv.get("attention_values") if gen.attention_values > 0 else None
+            return gen, _as_planes_tensor(cv["xy"], cv["xz"], cv["yz"]), palette, cv["viewdir_mapper_closure"]
+
+        rgb, depth, mask = render_viewdir(model_for, height, width, cam, focal, center, bbox, S, randomize=randomize,
+                                          white_background=dataset_config["white_background"],
+                                          fine_sampling=args.fine_sampling, force_no_cam_grad=force_no_cam_grad,
+                                          zbuffer_depth=zbuffer_depth, scene_range=dataset_config["scene_range"])
+        return rgb, depth, mask, None, None, box["outs"]
+
     def render(target_model, height, width, tform_cam2world, focal_length, center, bbox, model_input,
                depth_samples_per_ray, randomize=True, compute_normals=False, compute_semantics=False,
                compute_coords=False, extra_model_outputs=[], extra_model_inputs={},
                force_no_cam_grad=False):
         if args.use_viewdir:
-            raise NotImplementedError("nfi_b200.render: use_viewdir is not covered (SURVEY.md 8(f) N4)")
+            if compute_normals or compute_semantics or compute_coords:
+                raise NotImplementedError("nfi_b200.render: normals / semantics / coords maps with use_viewdir")
+            return _render_with_viewdir(target_model, height, width, tform_cam2world, focal_length, center, bbox,
+                                        model_input, depth_samples_per_ray, randomize, extra_model_outputs,
+                                        extra_model_inputs, force_no_cam_grad)
         if compute_normals:
             assert args.use_sdf                    # run.py:226
         # The generator still produces planes and attention values (StyleGAN2 synthesis, out of

@@ -12,15 +12,18 @@ import ref_loader
 
 
 def build_generator(device="cpu", attention_values=10, use_sdf=True, scene_range=1.4, seed=0,
-                    sdf_shift=-1.0):
+                    sdf_shift=-1.0, use_viewdir=False):
     """Random-init p3d_car-style generator (run.py:560-574 `create_model`).  The SDF bias is shifted so
     that the rendered mask is non-trivial at random init (mean SDF ~ +0.65 otherwise: empty scene; -1.0 gives a mask mean of ~0.37)."""
     m = ref_loader.modules()
     torch.manual_seed(seed)
-    G = m.generator.Generator(512, scene_range, attention_values=attention_values, use_viewdir=False,
+    G = m.generator.Generator(512, scene_range, attention_values=attention_values, use_viewdir=use_viewdir,
                               use_encoder=False, use_sdf=use_sdf)
     with torch.no_grad():
         G.decoder.net[2].bias[0] += sdf_shift
+        if use_viewdir:        # the output layer of the mapper is zero-initialised (generator.py:219-220): constant colours
+            G.viewdir_mapper.output.weight.normal_()
+            G.viewdir_mapper.output.bias.normal_(std=0.1)
     return G.to(device)
 
 

@@ -264,3 +264,36 @@ def test_make_render_two_threads_two_streams(cuda_setup):
         assert rel_err(results[i]["d_ws"].cpu(), solo[i]["d_ws"].cpu()) < TOL, i
         for k in ("d_cam", "d_focal"):
             assert rel_err(results[i][k].cpu(), solo[i][k].cpu()) < 5e-3, (i, k)
+
+
+@pytest.mark.gpu
+def test_make_render_view_direction_branch_vs_reference():
+    """SURVEY.md 8(f) N4 (CARLA, use_viewdir): make_render's hybrid path (library kernels for rays / sampling / gather +
+    decoder MLP / compositing, PyTorch for the per-ray modulation and the heads) against the reference's `render` on
+    the real Generator with its ViewDirectionMapper -- images and gradients to ws, pose, focal, beta, alpha."""
+    from nfi_b200 import _lib, render as R
+    _lib.lib()
+    torch.backends.cuda.matmul.allow_tf32 = False
+    torch.backends.cudnn.allow_tf32 = False
+    import ref_generator as rg
+    cfg = {"scene_range": 3.0, "white_background": True}            # data/loaders.py:72-83 (carla)
+    G = rg.build_generator("cuda", scene_range=3.0, use_viewdir=True, sdf_shift=-0.9)
+    G.requires_grad_(True)
+    B, HW = 2, 32
+    ws = rg.make_ws(B, "cuda")
+    cam, focal = _cams(rg, B, "cuda")
+    cam = cam.clone()
+    cam[:, :3, 3] *= 3.0 / 1.4
+    target = torch.rand(B, HW, HW, 3, device="cuda", generator=torch.Generator("cuda").manual_seed(3)) * 2 - 1
+    ref_render, _ = ref_loader.lift_render("run.py", scene_range=3.0, white_background=True, use_viewdir=True)
+    ours = R.make_render(rg.args_ns(use_viewdir=True), cfg)
+    ref = _run(ref_render, G, ws, cam, focal, HW, True, 11, target)
+    got = _run(ours, G, ws, cam, focal, HW, True, 11, target)
+    _assert_close(got, ref, pose_tol=5e-3)
+    # the mapper's own parameters get their gradient too
+    def mapper_grad(render):
+        torch.manual_seed(11)
+        out = render(G, HW, HW, cam, focal, None, None, ws, 64, randomize=True, extra_model_inputs={"freeze_noise": True})
+        return torch.autograd.grad((out[0] - target).abs().mean(), [G.viewdir_mapper.output.weight, G.viewdir_mapper.fc0.weight])
+    for a, b in zip(mapper_grad(ours), mapper_grad(ref_render)):
+        assert rel_err(a.cpu(), b.cpu()) < 5e-4
