@@ -16,6 +16,20 @@
 //   h_full[c]     E -> MMA              H (hi, lo) of set c written to TMEM, D0 of set c consumed
 //   d1_full[c]    MMA(commit) -> E      layer 1 accumulators complete (also: H of set c is free again)
 //   meta_empty[m] E -> P                table m no longer needed
+//
+// Phase discipline (audited in round 2; a parity wait is sound only while the waiter is at most one phase behind):
+//   barrier        arrives                      waits                         why phase k + 1 cannot complete before the test of k
+//   meta_full[m]   group of tile it, every tile MMA + epilogue, every tile    meta_full(it + 8) needs meta_empty(it): MMA and all
+//                                                                             epilogue warps past tile it
+//   meta_empty[m]  MMA at once; epilogue when    producers, every tile        the next phase needs the producers' own meta_full(it + 8)
+//                  the tile's heads are done
+//   a_full[s]      group of tile it, every tile MMA, every tile               group(it + 3) first waits a_empty(it) <- MMA past its test
+//   a_empty[s]     MMA, every tile              producers, every tile         a_empty(it) needs a_full(it), posted after the test
+//   d0_full / h_full / d1_full [c]              self-counted over ACTIVE tiles; MMA(k + 2) waits h_full(k), epilogue(k + 2) d0_full(k + 2)
+// Liveness (the round-2 bug): the heads of active tile i run after the softplus of the next active tile, so that the
+// layer-1 MMAs are never waited for.  Deferring them to the next ACTIVE tile is not enough: meta_empty(i) is only
+// released by those heads, and after kNM - 1 idle tiles the producers wait for it while the epilogue waits for the
+// producers.  Both the MMA warp and the epilogue warps therefore complete the pending tile on the first idle tile.
 #pragma once
 #include "nfi_f2.cuh"
 #include "nfi_field_tc.cuh"
