@@ -259,7 +259,12 @@ def run_ours(args):
     if cfg.get("allreduce") and world > 1:
         ar_bufs = [torch.zeros(n, dtype=torch.float32, device=dev) for n in cfg["allreduce"]]
 
-    def allreduce_payloads(timed):
+    def allreduce_payloads(timed, outs=None):
+        if world > 1 and leaf_w and outs is not None:
+            # the decoder / beta / alpha gradients of this path: one flat bucket over NCCL (dist.allreduce_grads,
+            # the sum nn.DataParallel performs at run.py:636-644)
+            from nfi_b200.dist import allreduce_grads
+            allreduce_grads(list(outs[-len(leaf_w):]), params=[wdev[k] for k in leaf_w])
         if not ar_bufs:
             return
         ev = (torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True))
@@ -276,8 +281,7 @@ def run_ours(args):
     torch.manual_seed(1234 + rank)
     n_warm = 1 if args.e2e_only else args.warmup
     for _ in range(n_warm):
-        step(*[t.detach() for t in resident])
-        allreduce_payloads(False)
+        allreduce_payloads(False, step(*[t.detach() for t in resident]))
     barrier()
     sampler = ClockSampler(local)
     if rank == 0:
@@ -289,8 +293,7 @@ def run_ours(args):
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
     for _ in range(args.steps):
-        step(*[t.detach() for t in resident])
-        allreduce_payloads(True)
+        allreduce_payloads(True, step(*[t.detach() for t in resident]))
     e1.record()
     barrier()
     _lib.PROFILE.stop()
