@@ -448,6 +448,108 @@ wgrad_reduce_kernel(const float* __restrict__ st_f, const float* __restrict__ st
   }
 }
 
+// The same reduction with the rows brought in by TMA bulk copies (cp.async.bulk, one per array and chunk: 16 + 16 + 8 + 4 KB
+// of contiguous rows) into a two-stage shared-memory ring, completion on mbarriers: no load instructions, no shared-memory
+// stores and no address arithmetic in the threads, and chunk i + 1 lands while chunk i is reduced.  Rows of samples that
+// took no part hold whatever the workspace held: they are skipped by their validity flag (uniform per row).
+struct WgTmaSmem {
+  WgSmem st[2];
+  int ok[2][kWgChunk];
+  uint64_t full[2];
+};
+
+__device__ __forceinline__ void wg_tma_issue(WgTmaSmem& sm, int s, const float* st_f, const float* st_h, const float* st_dh,
+                                             const float* st_dy, int64_t s0, int64_t n) {
+  const uint32_t rows = (uint32_t)((n - s0) < kWgChunk ? (n - s0) : kWgChunk);
+  nfi_tc::fence_proxy_async();                         // the stage was read through the generic proxy
+  nfi_tc::mbar_arrive_expect_tx(&sm.full[s], rows * (64 + 64 + 32 + 16) * 4);
+  nfi_tc::bulk_g2s(sm.st[s].dh, st_dh + s0 * 64, rows * 256, &sm.full[s]);
+  nfi_tc::bulk_g2s(sm.st[s].h, st_h + s0 * 64, rows * 256, &sm.full[s]);
+  nfi_tc::bulk_g2s(sm.st[s].f, st_f + s0 * 32, rows * 128, &sm.full[s]);
+  nfi_tc::bulk_g2s(sm.st[s].dy, st_dy + s0 * 16, rows * 64, &sm.full[s]);
+}
+
+__global__ void __launch_bounds__(kWgThreads)
+wgrad_reduce_tma_kernel(const float* __restrict__ st_f, const float* __restrict__ st_h, const float* __restrict__ st_dh,
+                        const float* __restrict__ st_dy, const unsigned char* __restrict__ st_ok, int64_t n, int n_out,
+                        float* __restrict__ g_params) {
+  extern __shared__ __align__(128) unsigned char wg_raw[];
+  WgTmaSmem& sm = *reinterpret_cast<WgTmaSmem*>(wg_raw);
+  const int tid = threadIdx.x, warp = tid >> 5;
+  if (tid == 0) { nfi_tc::mbar_init(&sm.full[0], 1); nfi_tc::mbar_init(&sm.full[1], 1); nfi_tc::mbar_fence_init(); }
+  __syncthreads();
+  float acc[16];
+#pragma unroll
+  for (int i = 0; i < 16; ++i) acc[i] = 0.f;
+  float bias = 0.f, bias1 = 0.f;
+  const int jb = (tid & 127) >> 3, kb = tid & 7;
+  const int ob = (tid - 128) >> 4, j1 = (tid - 128) & 15;
+  const int64_t nchunks = (n + kWgChunk - 1) / kWgChunk;
+  const int64_t first = blockIdx.x, stride = gridDim.x;
+  if (tid == 0) {
+    if (first < nchunks) wg_tma_issue(sm, 0, st_f, st_h, st_dh, st_dy, first * kWgChunk, n);
+    if (first + stride < nchunks) wg_tma_issue(sm, 1, st_f, st_h, st_dh, st_dy, (first + stride) * kWgChunk, n);
+  }
+  int it = 0;
+  for (int64_t ch = first; ch < nchunks; ch += stride, ++it) {
+    const int s = it & 1;
+    const int64_t s0 = ch * kWgChunk;
+    if (tid < kWgChunk) sm.ok[s][tid] = (s0 + tid < n && st_ok[s0 + tid] != 0) ? 1 : 0;
+    nfi_tc::mbar_wait(&sm.full[s], (it >> 1) & 1);
+    __syncthreads();
+    const WgSmem& st = sm.st[s];
+    const int* ok = sm.ok[s];
+    if (warp < 6) {
+      const float* gsrc = warp < 4 ? &st.dh[0][4 * jb] : &st.dy[0][4 * ob];
+      const float* xsrc = warp < 4 ? &st.f[0][4 * kb] : &st.h[0][4 * j1];
+      const int gld = warp < 4 ? 64 : 16, xld = warp < 4 ? 32 : 64;
+#pragma unroll 4
+      for (int r = 0; r < kWgChunk; ++r) {
+        if (!ok[r]) continue;
+        const float4 g = *reinterpret_cast<const float4*>(gsrc + r * gld);
+        const float4 x = *reinterpret_cast<const float4*>(xsrc + r * xld);
+        acc[0] = fmaf(g.x, x.x, acc[0]); acc[1] = fmaf(g.x, x.y, acc[1]); acc[2] = fmaf(g.x, x.z, acc[2]); acc[3] = fmaf(g.x, x.w, acc[3]);
+        acc[4] = fmaf(g.y, x.x, acc[4]); acc[5] = fmaf(g.y, x.y, acc[5]); acc[6] = fmaf(g.y, x.z, acc[6]); acc[7] = fmaf(g.y, x.w, acc[7]);
+        acc[8] = fmaf(g.z, x.x, acc[8]); acc[9] = fmaf(g.z, x.y, acc[9]); acc[10] = fmaf(g.z, x.z, acc[10]); acc[11] = fmaf(g.z, x.w, acc[11]);
+        acc[12] = fmaf(g.w, x.x, acc[12]); acc[13] = fmaf(g.w, x.y, acc[13]); acc[14] = fmaf(g.w, x.z, acc[14]); acc[15] = fmaf(g.w, x.w, acc[15]);
+      }
+    } else {
+      const int j = tid - 192;
+#pragma unroll 8
+      for (int r = 0; r < kWgChunk; ++r) {
+        if (!ok[r]) continue;
+        bias += st.dh[r][j];
+        if (j < 16) bias1 += st.dy[r][j];
+      }
+    }
+    __syncthreads();                                   // stage s is free: refill it with the chunk two steps ahead
+    const int64_t nxt = ch + 2 * stride;
+    if (tid == 0 && nxt < nchunks) wg_tma_issue(sm, s, st_f, st_h, st_dh, st_dy, nxt * kWgChunk, n);
+  }
+  const float g0 = (float)(1.0 / sqrt((double)nfi_mlp::kC)), g1 = (float)(1.0 / sqrt((double)nfi_mlp::kH));
+  float* gW0 = g_params;
+  float* gb0 = gW0 + NFI_HID * NFI_C;
+  float* gW1 = gb0 + NFI_HID;
+  float* gb1 = gW1 + n_out * NFI_HID;
+  if (warp < 4) {
+#pragma unroll
+    for (int a = 0; a < 4; ++a)
+#pragma unroll
+      for (int c = 0; c < 4; ++c)
+        if (acc[4 * a + c] != 0.f) atomicAdd(&gW0[(4 * jb + a) * NFI_C + 4 * kb + c], acc[4 * a + c] * g0);
+  } else if (warp < 6) {
+#pragma unroll
+    for (int a = 0; a < 4; ++a)
+#pragma unroll
+      for (int c = 0; c < 4; ++c)
+        if (4 * ob + a < n_out && acc[4 * a + c] != 0.f) atomicAdd(&gW1[(4 * ob + a) * NFI_HID + 4 * j1 + c], acc[4 * a + c] * g1);
+  } else {
+    const int j = tid - 192;
+    if (bias != 0.f) atomicAdd(&gb0[j], bias);
+    if (j < n_out && bias1 != 0.f) atomicAdd(&gb1[j], bias1);
+  }
+}
+
 static inline size_t wg_align(size_t v) { return (v + 255) & ~(size_t)255; }
 
 }  // namespace nfi_ftc
@@ -499,8 +601,19 @@ extern "C" int nfi_field_bwd_train(const NfiField* field, const float* planes_cl
   NFI_CHECK_LAUNCH("field_bwd_ws_kernel (training path)");
   const int64_t nchunks = (n + kWgChunk - 1) / kWgChunk;
   const int64_t cap = (int64_t)nfi_sm_count() * 4;
+#ifdef NFI_WGRAD_NO_TMA
   wgrad_reduce_kernel<<<(int)(nchunks < cap ? nchunks : cap), kWgThreads, 0, st>>>(
       a.st_f, a.st_h, a.st_dh, a.st_dy, a.st_ok, n, a.f.n_out, g_params);
+#else
+  {
+    const int wg_smem = (int)sizeof(WgTmaSmem);
+    rc = nfi_set_smem_once((const void*)wgrad_reduce_tma_kernel, wg_smem, "nfi_field_bwd_train");
+    if (rc) return rc;
+    const int64_t cap2 = (int64_t)nfi_sm_count() * 2;            // 2 CTAs of 92 KB per SM
+    wgrad_reduce_tma_kernel<<<(int)(nchunks < cap2 ? nchunks : cap2), kWgThreads, wg_smem, st>>>(
+        a.st_f, a.st_h, a.st_dh, a.st_dy, a.st_ok, n, a.f.n_out, g_params);
+  }
+#endif
   NFI_CHECK_LAUNCH("wgrad_reduce_kernel");
   return NFI_OK;
 }
