@@ -160,6 +160,20 @@ int nfi_field_bwd_train(const NfiField* field, const float* planes_cl, const flo
 int nfi_decoder_mlp_fwd(const NfiField* field, const float* feat, int64_t n, float* y, float* hpre,
                         nfi_stream_t stream);
 
+/* ---- N2: the regulariser path (models/generator.py:505-585; lib/ops.py:58-120 `grid_sample2d`, the
+ *      double-differentiable sampler behind TriplanarDecoder.forward(requires_double_backward=True)).
+ * coords [B, n_per_image, 3] in box units ([-1, 1], NOT clamped: lib/ops.py:69-70), gy [B, n_per_image, n_out] the
+ * upstream gradient of the raw decoder output -> gx [B, n_per_image, 3] = J^T gy, the gradient w.r.t. the coordinates
+ * (the reference's torch.autograd.grad(sdf.sum(), bins_in, create_graph=True), generator.py:533-536).
+ * _bwd is its backward (the double backward): gg [B, n_per_image, 3] -> ACCUMULATING g_planes_cl, g_W0 [64,32],
+ * g_b0 [64], g_W1 [n_out,64] (any may be NULL; caller zero-fills).  fp32 planes only. */
+int nfi_decoder_gradx_fwd(const NfiField* field, const float* planes_cl, int B, int Hp, int Wp,
+                          const float* coords, const float* gy, int64_t n_per_image, float* gx,
+                          nfi_stream_t stream);
+int nfi_decoder_gradx_bwd(const NfiField* field, const float* planes_cl, int B, int Hp, int Wp,
+                          const float* coords, const float* gy, const float* gg, int64_t n_per_image,
+                          float* g_planes_cl, float* g_W0, float* g_b0, float* g_W1, nfi_stream_t stream);
+
 /* ---- A7: render_volume_density_weights_only (lib/nerf_utils.py:166-182) + EG3D smoothing
  *      (run.py:266-272, smooth != 0).  sigma is read with stride `sigma_stride` floats. ----------- */
 int nfi_weights_only(const float* sigma, int sigma_stride, const float* dirs, const float* z,

@@ -64,6 +64,8 @@ _SIGS = {
     "nfi_field_bwd_train_workspace_bytes": (ctypes.c_size_t, [c_int64]),
     "nfi_field_bwd_train": (c_int, [POINTER(NfiField), _P, _P, c_int, c_int, c_int, _P, _P, _P, c_int64, c_int, c_int,
                                     _P, _P, _P, _P, _P, _P, ctypes.c_size_t, _P]),
+    "nfi_decoder_gradx_fwd": (c_int, [POINTER(NfiField), _P, c_int, c_int, c_int, _P, _P, c_int64, _P, _P]),
+    "nfi_decoder_gradx_bwd": (c_int, [POINTER(NfiField), _P, c_int, c_int, c_int, _P, _P, _P, c_int64, _P, _P, _P, _P, _P]),
     "nfi_decoder_mlp_fwd": (c_int, [POINTER(NfiField), _P, c_int64, _P, _P, _P]),
     "nfi_weights_only": (c_int, [_P, c_int, _P, _P, c_int64, c_int, c_int, _P, _P]),
     "nfi_sample_pdf": (c_int, [_P, _P, c_int64, c_int, c_int, _P, _P, _P, _P]),

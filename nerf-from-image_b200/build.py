@@ -8,7 +8,7 @@ CSRC = os.path.join(HERE, "csrc")
 LIBDIR = os.path.join(HERE, "lib")
 LIB = os.path.join(LIBDIR, "libnfi_b200.so")
 SOURCES = ["nfi_api.cu", "nfi_rays.cu", "nfi_importance.cu", "nfi_composite.cu", "nfi_field_fwd.cu",
-           "nfi_field_bwd.cu", "nfi_mlp.cu", "nfi_render.cu", "nfi_pose.cu"]
+           "nfi_field_bwd.cu", "nfi_mlp.cu", "nfi_render.cu", "nfi_pose.cu", "nfi_sdfgrad.cu"]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
               "-Xcompiler", "-fPIC"]
 

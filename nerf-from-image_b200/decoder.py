@@ -73,9 +73,19 @@ def triplanar_decoder_forward(self, xy, xz, yz, coords, requires_double_backward
     """Replacement for `TriplanarDecoder.forward` (models/generator.py:301-331).
 
     `coords` [B, N, 1, 3] in box units -> {'features' [B,N,n_out-1], 'density_or_distance' [B,N,1]}.
-    The double-backward path (eikonal regulariser, generator.py:306-310) stays on the reference
-    implementation."""
+    The double-backward path (eikonal regulariser, generator.py:306-310, 505-585) runs on
+    ops.decoder_double_backward; only a use_viewdir decoder (33 outputs) on that path falls back
+    to the saved reference forward."""
     if requires_double_backward:
+        # SURVEY.md 8(f) N2: the eikonal regulariser differentiates the output w.r.t. the coordinates with
+        # create_graph=True (generator.py:533-536); ops.decoder_double_backward supports exactly that
+        assert xy.shape[1] == self.num_input_features == 32
+        planes_cl = ops.planes_to_channels_last(_as_planes_tensor(xy, xz, yz))
+        l0, l2 = self.net[0], self.net[2]
+        if xy.is_cuda and l2.weight.shape[0] <= 16:
+            B = xy.shape[0]
+            y = ops.decoder_double_backward(planes_cl, l0.weight, l0.bias, l2.weight, l2.bias, coords.reshape(B, -1, 3))
+            return {"features": y[..., 1:], "density_or_distance": y[..., :1]}
         return self._nfi_reference_forward(xy, xz, yz, coords, requires_double_backward)
     assert xy.shape[1] == self.num_input_features
     assert xz.shape[1] == self.num_input_features

@@ -381,6 +381,88 @@ def _field_bwd_train(field, pl, pal, B, Hp, Wp, o, d, zz, npi, S, img_w, g, g_pl
              None if gp2 is None else ptr(gp2[sl]), ptr(g_params), ptr(ws), ws_bytes)
 
 
+# ---------------------------------------------------------------------------------------------
+# N2  regulariser path: decoder output with a DIFFERENTIABLE coordinate gradient (double backward)
+#     models/generator.py:505-585, lib/ops.py:58-120 (grid_sample2d), TriplanarDecoder.forward(requires_double_backward=True)
+# ---------------------------------------------------------------------------------------------
+class _DecoderGradX(Function):
+    """gx = J^T gy: the gradient of the raw decoder output w.r.t. the query coordinates (box units), as the
+    reference obtains it with autograd.grad(..., create_graph=True) (generator.py:533-536).  Its backward -- the
+    double backward -- gives the gradients of any function of gx w.r.t. planes, W0, b0, W1 (hand-written kernel,
+    csrc/nfi_sdfgrad.cu).  No gradient flows to the coordinates or to gy from here (the reference's losses need none)."""
+
+    @staticmethod
+    def forward(ctx, planes_cl, W0, b0, W1, coords, gy):
+        pl, x, g = f32c(planes_cl), f32c(coords), f32c(gy)
+        B, _, Hp, Wp, _ = pl.shape
+        n = x.numel() // 3 // B
+        n_out = W1.shape[0]
+        field, keep = _lib.make_field_struct(W0, b0, W1, torch.zeros(n_out, device=pl.device), None, None,
+                                             n_out - 1 if n_out != 4 else 0, False, 1.0)
+        gx = _empty(pl, *x.shape)
+        call("nfi_decoder_gradx_fwd", pl, field, ptr(pl), B, Hp, Wp, ptr(x), ptr(g), n, ptr(gx))
+        ctx.save_for_backward(pl, keep[0], keep[1], keep[2], x, g)
+        return gx
+
+    @staticmethod
+    @once_differentiable
+    def backward(ctx, gg):
+        pl, W0, b0, W1, x, g = ctx.saved_tensors
+        B, _, Hp, Wp, _ = pl.shape
+        n = x.numel() // 3 // B
+        n_out = W1.shape[0]
+        need = ctx.needs_input_grad
+        field, keep = _lib.make_field_struct(W0, b0, W1, torch.zeros(n_out, device=pl.device), None, None,
+                                             n_out - 1 if n_out != 4 else 0, False, 1.0)
+        gpl = torch.zeros_like(pl) if need[0] else None
+        gW0 = torch.zeros_like(W0) if need[1] else None
+        gb0 = torch.zeros_like(b0) if need[2] else None
+        gW1 = torch.zeros_like(W1) if need[3] else None
+        call("nfi_decoder_gradx_bwd", pl, field, ptr(pl), B, Hp, Wp, ptr(x), ptr(g), ptr(f32c(gg)), n, ptr(gpl),
+             ptr(gW0), ptr(gb0), ptr(gW1))
+        return gpl, gW0, gb0, gW1, None, None
+
+
+class _DecoderDD(Function):
+    """Raw decoder output at explicit points whose backward is itself differentiable in the one way the reference
+    uses: the gradient w.r.t. the coordinates (`_DecoderGradX`).  The gradients w.r.t. planes and weights are the
+    ordinary first-order ones (nfi_field_bwd, raw-decoder mode)."""
+
+    @staticmethod
+    def forward(ctx, planes_cl, W0, b0, W1, b1, coords):
+        n_out = W1.shape[0]
+        cfg = FieldConfig(attention_values=(n_out - 1) if n_out != 4 else 0, use_sdf=False, scene_range=1.0)
+        with torch.no_grad():
+            y, _ = field_on_points(planes_cl, None, W0, b0, W1, b1, None, None, coords, cfg, mode=1)
+        ctx.save_for_backward(planes_cl, W0, b0, W1, b1, coords)
+        ctx.cfg = cfg
+        return y
+
+    @staticmethod
+    def backward(ctx, gy):
+        planes_cl, W0, b0, W1, b1, coords = ctx.saved_tensors
+        need = ctx.needs_input_grad
+        g_coords = None
+        if need[5]:
+            g_coords = _DecoderGradX.apply(planes_cl, W0, b0, W1, coords, gy)
+        grads = [None] * 5
+        if any(need[:5]):
+            with torch.enable_grad():
+                leaves = [t.detach().requires_grad_(need[i]) for i, t in enumerate((planes_cl, W0, b0, W1, b1))]
+                y, _ = field_on_points(leaves[0], None, leaves[1], leaves[2], leaves[3], leaves[4], None, None,
+                                       coords.detach(), ctx.cfg, mode=1)
+                wanted = [t for t, nd in zip(leaves, need[:5]) if nd]
+                got = torch.autograd.grad(y, wanted, gy.detach())
+            it = iter(got)
+            grads = [next(it) if nd else None for nd in need[:5]]
+        return (*grads, g_coords)
+
+
+def decoder_double_backward(planes_cl, W0, b0, W1, b1, coords):
+    """y [B,N,n_out] = decoder(coords) with a backward that supports create_graph=True w.r.t. `coords`."""
+    return _DecoderDD.apply(planes_cl, W0, b0, W1, b1, coords)
+
+
 def decoder_mlp(feat, W0, b0, W1, b1, want_hidden=False):
     """Decoder MLP alone on the tensor cores (forward only): feat [n,32] -> y [n,n_out]."""
     ft = f32c(feat.detach())
