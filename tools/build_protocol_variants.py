@@ -20,22 +20,26 @@ VARIANTS = {"newproto_delay": ("nfi_field_bwd.cu", COMMON),
 def build(force=False):
     B.build()
     hdrs = [os.path.join(B.CSRC, f) for f in os.listdir(B.CSRC) if f.endswith(".cuh")]
-    procs = []
+    hdrs.append(os.path.join(os.path.dirname(B.HERE), "include", "nfi_b200.h"))
+    main_objs = [os.path.join(B.LIBDIR, s.replace(".cu", ".o")) for s in B.SOURCES]
+    procs, relink = [], []
     for name, (SRC, flags) in VARIANTS.items():
         src = os.path.join(B.CSRC, SRC)
-        deps = [src] + hdrs
         lib = os.path.join(B.LIBDIR, "libnfi_b200_%s.so" % name)
-        if not force and not B._stale(lib, deps + [os.path.abspath(__file__)]):
-            continue
         o = os.path.join(B.LIBDIR, "proto_%s.o" % name)
-        cmd = [B._nvcc()] + B.NVCC_FLAGS + flags + ["-c", src, "-o", o]
-        procs.append((name, SRC, o, lib, subprocess.Popen(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT)))
-    for name, SRC, o, lib, p in procs:
+        if force or B._stale(o, [src, os.path.abspath(__file__)] + hdrs):
+            cmd = [B._nvcc()] + B.NVCC_FLAGS + flags + ["-c", src, "-o", o]
+            procs.append((name, subprocess.Popen(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT)))
+        relink.append((name, SRC, o, lib))
+    for name, p in procs:
         out = p.communicate()[0].decode()
         if p.returncode:
             raise RuntimeError("nvcc failed for %s:\n%s" % (name, out))
-        objs = [os.path.join(B.LIBDIR, s.replace(".cu", ".o")) if s != SRC else o for s in B.SOURCES]
-        subprocess.check_call([B._nvcc(), "-shared", "-o", lib] + objs)
+    for name, SRC, o, lib in relink:
+        # the variant is the shipped library with ONE object replaced: relink whenever any object is newer
+        objs = [m if os.path.basename(m) != SRC.replace(".cu", ".o") else o for m in main_objs]
+        if force or B._stale(lib, objs):
+            subprocess.check_call([B._nvcc(), "-shared", "-o", lib] + objs)
     return [os.path.join(B.LIBDIR, "libnfi_b200_%s.so" % n) for n in VARIANTS]
 
 
