@@ -255,8 +255,9 @@ class _Field(Function):
 
     @staticmethod
     def forward(ctx, planes_cl, palette, W0, b0, W1, b1, beta, alpha, origins, dirs, z, points,
-                cfg, mode, img_w, skip_oob, want_probs, sink=None, planes_bf16=None):
+                cfg, mode, img_w, skip_oob, want_probs, sink=None, planes_bf16=None, probs_grad=False):
         ctx.sink = sink
+        ctx.probs_grad = bool(probs_grad)
         pl = f32c(planes_cl)
         # bf16 mode: the kernels gather from `planes_bf16` (a bfloat16 copy of planes_cl, same layout);
         # planes_cl stays the autograd handle, so the plane gradient is fp32 like the master copy
@@ -294,16 +295,23 @@ class _Field(Function):
         ctx.cfg, ctx.mode, ctx.img_w, ctx.npi, ctx.S = cfg, mode, int(img_w), npi, S
         ctx.oshape = None if origins is None else origins.shape
         ctx.pshape = None if points is None else points.shape
+        ctx.probs = None
         if probs is not None:
-            ctx.mark_non_differentiable(probs)
+            if ctx.probs_grad:
+                ctx.probs = probs          # attention probabilities with a gradient (lib/nerf_utils.py:152-155)
+            else:
+                ctx.mark_non_differentiable(probs)
             return out, probs
         return out, None
 
     @staticmethod
     @once_differentiable
-    def backward(ctx, g_out, _g_probs):
+    def backward(ctx, g_out, g_probs):
         pl, pal, W0, b0, W1, b1, beta, alpha, o, d, zz, pts = ctx.saved_tensors
         cfg, mode = ctx.cfg, ctx.mode
+        if g_out is None:
+            lead = zz.shape if pts is None else pts.shape[:-1]
+            g_out = torch.zeros(*lead, 4 if mode == 0 else W1.shape[0], dtype=torch.float32, device=pl.device)
         need = ctx.needs_input_grad
         want_w = any(need[2:6])           # generator training (run.py:980-986)
         B, _, Hp, Wp, _ = pl.shape
@@ -331,6 +339,20 @@ class _Field(Function):
             call("nfi_field_bwd", pl, field, ptr(src), ptr(pal), B, Hp, Wp, ptr(o), ptr(d), ptr(zz), ptr(pts),
                  ctx.npi, ctx.S, mode, ctx.img_w, ptr(g), ptr(g_planes), ptr(g_pal), ptr(g_points),
                  ptr(g_params), int(want_w))
+        if g_probs is not None and ctx.probs is not None:
+            # gradient arriving at the attention probabilities (semantic map): softmax backward to the logits, then ONE
+            # more launch of the field backward in raw-decoder mode with that as the upstream gradient of the decoder
+            # output -- same planes / weights / points targets (the point gradient is overwritten by the kernel: summed here)
+            pr = ctx.probs
+            gpz = f32c(g_probs)
+            dlog = pr * (gpz - (pr * gpz).sum(-1, keepdim=True))
+            gy2 = torch.cat((torch.zeros_like(dlog[..., :1]), dlog), dim=-1).contiguous()
+            g_points2 = torch.empty_like(g_points) if g_points is not None else None
+            call("nfi_field_bwd", pl, field, ptr(src), None, B, Hp, Wp, ptr(o), ptr(d), ptr(zz), ptr(pts),
+                 ctx.npi, ctx.S, 1, ctx.img_w, ptr(gy2), ptr(g_planes), None, ptr(g_points2),
+                 ptr(g_params) if want_w else None, int(want_w))
+            if g_points is not None:
+                g_points = g_points + g_points2
         go = gd = gp = None
         if want_pts:
             if pts is None:
@@ -354,7 +376,7 @@ class _Field(Function):
                 gW1 = g_params[o1:o2].view_as(W1) if need[4] else None
                 gb1 = g_params[o2:base].view_as(b1) if need[5] else None
         return (ret_planes, g_pal, gW0, gb0, gW1, gb1, g_beta, g_alpha, go, gd, None, gp,
-                None, None, None, None, None, None, None)
+                None, None, None, None, None, None, None, None)
 
 
 TRAIN_WORKSPACE_CAP = 6 << 30     # bytes; larger batches go image chunk by image chunk (gradients accumulate)
@@ -482,11 +504,11 @@ def planes_bf16_copy(planes_cl):
 
 
 def field_on_rays(planes_cl, palette, W0, b0, W1, b1, beta, alpha, origins, dirs, z, cfg,
-                  img_w=0, skip_oob=False, want_probs=False, sink=None, planes_bf16=None):
+                  img_w=0, skip_oob=False, want_probs=False, sink=None, planes_bf16=None, probs_grad=False):
     """(sigma, r, g, b) [.., S, 4] for the samples o + d*z of every ray (no points tensor in HBM).
     `sink`: a PlaneGradSink shared with the other passes over the same planes_cl."""
     return _Field.apply(planes_cl, palette, W0, b0, W1, b1, beta, alpha, origins, dirs, z.detach(),
-                        None, cfg, 0, img_w, skip_oob, want_probs, sink, planes_bf16)
+                        None, cfg, 0, img_w, skip_oob, want_probs, sink, planes_bf16, probs_grad)
 
 
 def field_on_points(planes_cl, palette, W0, b0, W1, b1, beta, alpha, points, cfg, mode=0,

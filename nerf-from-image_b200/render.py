@@ -10,6 +10,7 @@ Two entry points:
 """
 from __future__ import annotations
 
+import contextlib
 from typing import Optional
 
 import torch
@@ -32,8 +33,9 @@ def render_planes(planes, palette, field: Field, height: int, width: int, tform_
     (+ aux dict).  `u_strat` [B,H,W,S] / `u_pdf` [B*H*W,S] override the uniforms that are
     otherwise drawn with torch.rand in the reference's order (nerf_utils.py:115, :204).
     compute_normals / compute_semantics / compute_coords (run.py:186-188) add the
-    forward-only maps aux["normals"] [B,H,W,3] and aux["semantics"] [B,H,W,A] (coords [B,H,W,3] take
-    the semantics slot, run.py:337-338); they imply `return_aux`.
+    maps aux["normals"] [B,H,W,3] (forward-only, as the reference detaches them) and aux["semantics"] [B,H,W,A]
+    (coords [B,H,W,3] take the semantics slot, run.py:337-338), the latter with gradients when autograd is on
+    (lib/nerf_utils.py:152-155); they imply `return_aux`.
     plane_dtype=torch.bfloat16 is the bf16 mode of the contract (1e-2 instead of 1e-4): the gather reads
     a bfloat16 copy of the planes (half the texel bytes); everything after the load, and every gradient,
     stays fp32.  Not available together with decoder weight gradients or the extra maps.
@@ -66,8 +68,13 @@ def render_planes(planes, palette, field: Field, height: int, width: int, tform_
     if compute_semantics:
         assert field.cfg.attention_values > 0      # run.py:229
     sink = ops.PlaneGradSink() if fine_sampling else None     # coarse + fine: one gradient buffer
+    # The semantic / coordinate maps carry gradients like the reference's (lib/nerf_utils.py:152-155 keeps the weights
+    # and the per-sample payload attached) when autograd is on; the evaluation callers run under no_grad and take the
+    # cheaper forward-only route.  Normals stay forward-only (the reference detaches them, generator.py:619-622).
+    grad_maps = torch.is_grad_enabled() and (compute_semantics or compute_coords)
     coarse, probs_c = ops.field_on_rays(planes_cl, palette, *wts, o_s, d_s, z_c, field.cfg, img_w=W,
-                                        skip_oob=not want_sem, want_probs=want_sem, sink=sink, planes_bf16=pl16)
+                                        skip_oob=not want_sem, want_probs=want_sem, sink=sink, planes_bf16=pl16,
+                                        probs_grad=grad_maps and want_sem)
     nrm_c = ops.sdf_normals_on_rays(planes_cl, *wts[:4], o_s, d_s, z_c, field.cfg, img_w=W) \
         if compute_normals else None
     aux = {"origins": o, "dirs": d, "near": near, "far": far, "z_coarse": z_c, "normals": None,
@@ -81,7 +88,8 @@ def render_planes(planes, palette, field: Field, height: int, width: int, tform_
         else:
             z_f = z_fine.detach().reshape(z_c.shape).contiguous().float()
         fine, probs_f = ops.field_on_rays(planes_cl, palette, *wts, o_s, d_s, z_f, field.cfg, img_w=W,
-                                          skip_oob=not want_sem, want_probs=want_sem, sink=sink, planes_bf16=pl16)
+                                          skip_oob=not want_sem, want_probs=want_sem, sink=sink, planes_bf16=pl16,
+                                          probs_grad=grad_maps and want_sem)
         # A9 + A10
         rgb, depth, mask, perm, z_sorted = ops.merge_composite(
             coarse, fine, z_c, z_f, d, white_background, cam.detach() if zbuffer_depth else None)
@@ -89,20 +97,22 @@ def render_planes(planes, palette, field: Field, height: int, width: int, tform_
         if extras:
             # N1: per-sample payloads in depth order (run.py:312-335) and their maps
             # (nerf_utils.py:148-161); forward-only, from the stage-level compositing kernel
-            with torch.no_grad():
+            with (contextlib.nullcontext() if grad_maps else torch.no_grad()):
+                det = (lambda t: t) if grad_maps else (lambda t: t.detach())
+
                 def sort(c, f):
                     both = torch.cat((c, f), dim=-2)
                     return both.gather(-2, perm.long().unsqueeze(-1).expand(*perm.shape, both.shape[-1]))
                 nrm = sem = None
                 if compute_normals:
-                    nrm_f = ops.sdf_normals_on_rays(planes_cl, *wts[:4], o_s, d_s, z_f, field.cfg, img_w=W)
-                    nrm = sort(nrm_c, nrm_f)
+                    with torch.no_grad():
+                        nrm_f = ops.sdf_normals_on_rays(planes_cl, *wts[:4], o_s, d_s, z_f, field.cfg, img_w=W)
+                        nrm = sort(nrm_c, nrm_f)
                 if compute_coords:
-                    sem = sort(ops.points_on_rays(o_s.detach(), d_s.detach(), z_c),
-                               ops.points_on_rays(o_s.detach(), d_s.detach(), z_f))
+                    sem = sort(ops.points_on_rays(det(o_s), det(d_s), z_c), ops.points_on_rays(det(o_s), det(d_s), z_f))
                 elif compute_semantics:
                     sem = sort(probs_c, probs_f)
-                both = sort(coarse.detach(), fine.detach())
+                both = sort(det(coarse), det(fine))
                 _, _, _, nmap, smap = ops.composite(both[..., 0], both[..., 1:], d.detach(), z_sorted, nrm,
                                                     sem, white_background)
                 aux.update(normals=nmap, semantics=smap)

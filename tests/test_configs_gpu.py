@@ -108,3 +108,51 @@ def test_config_full_size_vs_reference_render_on_gpu(cid, B):
         assert frac < 1e-3, "image %d: %.3g of the texels off by more than %g of the max-norm" % (b, frac, TOL)
         l2 = float((gp_o[b] - gp_r[b]).norm() / gp_r[b].norm())
         assert l2 < 5e-3, "image %d: relative L2 error %.3g" % (b, l2)
+
+
+@pytest.mark.parametrize("which", ["semantics", "coords"])
+def test_semantic_and_coordinate_maps_carry_gradients_like_the_reference(which):
+    """lib/nerf_utils.py:152-155 keeps the compositing weights and the per-sample payload attached, so a loss on the
+    semantic map (attention probabilities) or on the coordinate map (run.py:337-338) has gradients to planes, decoder
+    output, pose and focal.  render_planes(compute_semantics / compute_coords) under autograd against the reference's
+    own `render` on the GPU."""
+    import bench
+    import ref_model
+    from nfi_b200 import decoder, render
+    torch.backends.cuda.matmul.allow_tf32 = False
+    torch.backends.cudnn.allow_tf32 = False
+    cfg = bench.CONFIGS["2"]
+    B, H, W, S = 2, 32, 32, 64
+    inp = bench.make_inputs(cfg, B, res=H)
+    fd = inp["field"]
+    dev = "cuda"
+    base = {k: inp[k].to(dev) for k in ("planes", "palette", "cam", "focal")}
+    flags = dict(compute_semantics=True) if which == "semantics" else dict(compute_coords=True)
+    g = torch.Generator(device=dev).manual_seed(3)
+    wmap = torch.randn(B, H, W, 10 if which == "semantics" else 3, device=dev, generator=g)
+
+    def leaves():
+        return {k: base[k].clone().requires_grad_() for k in ("planes", "cam", "focal")}
+
+    def loss_of(rgb, smap):
+        return (smap * wmap).sum() / (H * W) + 0.1 * rgb.abs().mean()
+
+    lv = leaves()
+    ref_render = ref_model.reference_render_fn("run.py", scene_range=cfg["scene_range"], white_background=False)
+    G = ref_model.reference_generator(lv["planes"], fd, cfg["scene_range"]).to(dev)
+    torch.manual_seed(99)
+    out = ref_render(G, H, W, lv["cam"], lv["focal"], None, None, torch.zeros(B, 15, 512, device=dev), S, randomize=True,
+                     extra_model_inputs={"attention_values": base["palette"]}, **flags)
+    ref_map = out[4].detach()
+    ref_g = torch.autograd.grad(loss_of(out[0], out[4]), list(lv.values()))
+    lv = leaves()
+    wts = {k: fd[k].to(dev) for k in WK}
+    fld = decoder.Field(*[wts[k] for k in WK], cfg["scene_range"], 10, True)
+    torch.manual_seed(99)
+    rgb, depth, mask, aux = render.render_planes(lv["planes"], base["palette"], fld, H, W, lv["cam"], lv["focal"], None, None,
+                                                 S, randomize=True, **flags)
+    got_g = torch.autograd.grad(loss_of(rgb, aux["semantics"]), list(lv.values()))
+    assert rel_err(aux["semantics"].detach().cpu(), ref_map.cpu()) < TOL
+    for k, a, b in zip(lv, got_g, ref_g):
+        tol = POSE_TOL if k in ("cam", "focal") else 5e-4
+        assert rel_err(a.cpu(), b.cpu()) < tol, (k, rel_err(a.cpu(), b.cpu()))
