@@ -56,7 +56,8 @@ typedef struct NfiField {
   float scene_range;        /* points are divided by this (generator.py:604); 1.0 for raw decoder coords */
   int32_t planes_bf16;      /* bf16 mode (1e-2 contract): planes_cl points to a bfloat16 copy of the
                              * channels-last planes (same texel order, 64 bytes per texel); plane gradients
-                             * stay fp32.  nfi_field_fwd / nfi_field_bwd without weight gradients only. */
+                             * stay fp32.  nfi_field_fwd, nfi_field_bwd without weight gradients, and
+                             * nfi_field_bwd_train (weight gradients). */
 } NfiField;
 
 int nfi_version(void);

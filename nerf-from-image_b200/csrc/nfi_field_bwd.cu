@@ -574,7 +574,6 @@ extern "C" int nfi_field_bwd_train(const NfiField* field, const float* planes_cl
   NFI_REQUIRE(nfi_aligned16(g_out), NFI_ERR_ALIGNMENT, "nfi_field_bwd_train: g_out must be 16-byte aligned");
   NFI_REQUIRE(!g_planes_cl || nfi_aligned16(g_planes_cl), NFI_ERR_ALIGNMENT, "nfi_field_bwd_train: g_planes must be 16-byte aligned");
   NFI_REQUIRE((((uintptr_t)workspace) & 255u) == 0, NFI_ERR_ALIGNMENT, "nfi_field_bwd_train: workspace must be 256-byte aligned");
-  NFI_REQUIRE(!field->planes_bf16, NFI_ERR_UNSUPPORTED, "nfi_field_bwd_train: not available with a bf16 plane copy");
   const int64_t n = a.n_total;
   NFI_REQUIRE(workspace_bytes >= nfi_field_bwd_train_workspace_bytes(n), NFI_ERR_BAD_ARG,
               "nfi_field_bwd_train: workspace of %zu bytes, %zu needed", workspace_bytes,
@@ -589,15 +588,15 @@ extern "C" int nfi_field_bwd_train(const NfiField* field, const float* planes_cl
   cudaStream_t st = nfi_cu(stream);
   const int grid = field_grid_chunks(a);
   const int smem = (int)sizeof(BwSmem);
-  if (g_points) {
-    rc = nfi_set_smem_once((const void*)field_bwd_ws_kernel<false, 0, true, false, true>, smem, "nfi_field_bwd_train");
-    if (rc) return rc;
-    field_bwd_ws_kernel<false, 0, true, false, true><<<grid, kBwThreads, smem, st>>>(a);
-  } else {
-    rc = nfi_set_smem_once((const void*)field_bwd_ws_kernel<false, 0, false, false, true>, smem, "nfi_field_bwd_train");
-    if (rc) return rc;
-    field_bwd_ws_kernel<false, 0, false, false, true><<<grid, kBwThreads, smem, st>>>(a);
-  }
+#define NFI_LAUNCH_TRAIN(W, H)                                                                                     \
+  do {                                                                                                           \
+    rc = nfi_set_smem_once((const void*)field_bwd_ws_kernel<false, 0, W, H, true>, smem, "nfi_field_bwd_train"); \
+    if (rc) return rc;                                                                                           \
+    field_bwd_ws_kernel<false, 0, W, H, true><<<grid, kBwThreads, smem, st>>>(a);                                \
+  } while (0)
+  if (a.f.planes_bf16) { if (g_points) NFI_LAUNCH_TRAIN(true, true); else NFI_LAUNCH_TRAIN(false, true); }
+  else                 { if (g_points) NFI_LAUNCH_TRAIN(true, false); else NFI_LAUNCH_TRAIN(false, false); }
+#undef NFI_LAUNCH_TRAIN
   NFI_CHECK_LAUNCH("field_bwd_ws_kernel (training path)");
   const int64_t nchunks = (n + kWgChunk - 1) / kWgChunk;
   const int64_t cap = (int64_t)nfi_sm_count() * 4;

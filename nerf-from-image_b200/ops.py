@@ -332,8 +332,8 @@ class _Field(Function):
         want_params = want_w or (cfg.use_sdf and mode == 0 and (need[6] or need[7]))
         g_params = torch.zeros(sum(_param_sizes(n_out)), dtype=torch.float32, device=pl.device) \
             if want_params else None
-        if want_w and pts is None and mode == 0 and ctx.planes_bf16 is None:
-            _field_bwd_train(field, pl, pal, B, Hp, Wp, o, d, zz, ctx.npi, ctx.S, ctx.img_w, g, g_planes, g_pal,
+        if want_w and pts is None and mode == 0:
+            _field_bwd_train(field, src, pal, B, Hp, Wp, o, d, zz, ctx.npi, ctx.S, ctx.img_w, g, g_planes, g_pal,
                              g_points, g_params)
         else:
             call("nfi_field_bwd", pl, field, ptr(src), ptr(pal), B, Hp, Wp, ptr(o), ptr(d), ptr(zz), ptr(pts),

@@ -38,7 +38,7 @@ def render_planes(planes, palette, field: Field, height: int, width: int, tform_
     (lib/nerf_utils.py:152-155); they imply `return_aux`.
     plane_dtype=torch.bfloat16 is the bf16 mode of the contract (1e-2 instead of 1e-4): the gather reads
     a bfloat16 copy of the planes (half the texel bytes); everything after the load, and every gradient,
-    stays fp32.  Not available together with decoder weight gradients or the extra maps.
+    stays fp32.  Not available together with the extra maps.
     z_fine [B,H,W,S] (test hook): use these fine depths instead of running A7 + A8 -- lets a parity test
     feed the reference's own importance samples, so that what remains is the differentiable path alone."""
     H, W, S = int(height), int(width), int(depth_samples_per_ray)

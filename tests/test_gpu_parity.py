@@ -426,11 +426,14 @@ def test_render_bf16_mode_contract(nfi):
         assert v < (BF16_POSE_TOL if k in ("d_cam", "d_focal") else BF16_TOL), (k, v, errs)
 
 
-def test_bf16_planes_reject_weight_gradients(nfi):
-    """Decoder weight gradients run in the kernel that has no bf16 gather: a loud error, not a silent fp32 path."""
-    from nfi_b200 import _lib
-    with pytest.raises(_lib.NfiError):
-        _oracle_vs_cuda(nfi, 1, 16, 16, 64, 64, True, True, False, False, seed=7, plane_dtype=torch.bfloat16)
+def test_bf16_planes_with_weight_gradients(nfi):
+    """Round 2: the generator-training gradient set runs on the warp-specialised kernel (nfi_field_bwd_train), which
+    has the bf16 gather -- a bf16 plane copy and decoder weight gradients together, held to the fp32 tolerance
+    against the oracle fed with the same rounded planes (round 1 rejected the combination)."""
+    errs, flips, n = _oracle_vs_cuda(nfi, 2, 16, 32, 64, 64, True, True, False, False, seed=7,
+                                     plane_dtype=torch.bfloat16, oracle_bf16_planes=True)
+    assert {"d_W0", "d_b0", "d_W1", "d_b1", "d_beta", "d_alpha"} <= set(errs)
+    _check(errs, flips, n)
 
 
 # ---------------------------------------------------------------- BASELINE.json sizes
