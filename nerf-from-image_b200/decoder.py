@@ -79,10 +79,10 @@ def triplanar_decoder_forward(self, xy, xz, yz, coords, requires_double_backward
     if requires_double_backward:
         # the eikonal regulariser differentiates the output w.r.t. the coordinates with
         # create_graph=True (generator.py:533-536); ops.decoder_double_backward supports exactly that
-        assert xy.shape[1] == self.num_input_features == 32
-        planes_cl = ops.planes_to_channels_last(_as_planes_tensor(xy, xz, yz))
         l0, l2 = self.net[0], self.net[2]
-        if xy.is_cuda and l2.weight.shape[0] <= 16:
+        if xy.is_cuda and l2.weight.shape[0] <= 16:       # CPU callers and 33-output (use_viewdir) decoders: reference path
+            assert xy.shape[1] == self.num_input_features == 32
+            planes_cl = ops.planes_to_channels_last(_as_planes_tensor(xy, xz, yz))
             B = xy.shape[0]
             y = ops.decoder_double_backward(planes_cl, l0.weight, l0.bias, l2.weight, l2.bias, coords.reshape(B, -1, 3))
             return {"features": y[..., 1:], "density_or_distance": y[..., :1]}

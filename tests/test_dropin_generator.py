@@ -110,6 +110,26 @@ def test_patched_decoder_forward_gets_real_planes(monkeypatch):
     assert out["sigma"].shape == (B, 128) and out["rgb"].shape == (B, 128, 3)   # flat, generator.py:604-608
 
 
+def test_patched_decoder_double_backward_on_cpu_keeps_the_reference_path():
+    """N2 on the host: the kernels are CUDA-only, so a CPU caller of the regulariser path (dataset tooling, unit tests of the
+    reference) must still get the reference's own double-differentiable sampler through the replaced forward."""
+    G, rg = _gen("cpu")
+    ws = rg.make_ws(1)
+
+    def eik():
+        torch.manual_seed(3)
+        G.train()
+        try:
+            return float(G(None, ws, ["sdf_eikonal_loss"], {"freeze_noise": True})["sdf_eikonal_loss"].sum())
+        finally:
+            G.eval()
+
+    ref = eik()
+    with rg.installed_modules():
+        got = eik()
+    assert ref > 0 and abs(got - ref) <= 1e-6 * abs(ref)
+
+
 def test_pending_hit_counters_are_per_thread():
     from nfi_b200 import ops
     ops._PENDING.hits.append("main")
