@@ -80,7 +80,10 @@ def triplanar_decoder_forward(self, xy, xz, yz, coords, requires_double_backward
         # the eikonal regulariser differentiates the output w.r.t. the coordinates with
         # create_graph=True (generator.py:533-536); ops.decoder_double_backward supports exactly that
         l0, l2 = self.net[0], self.net[2]
-        if xy.is_cuda and l2.weight.shape[0] <= 16:       # CPU callers and 33-output (use_viewdir) decoders: reference path
+        if not xy.is_cuda:
+            from ._lib import NfiError
+            raise NfiError("nfi_b200 ops run on CUDA tensors only (got %s); there is no CPU path" % xy.device)
+        if l2.weight.shape[0] <= 16:       # a 33-output (use_viewdir) decoder on this path stays on the reference's PyTorch ops
             assert xy.shape[1] == self.num_input_features == 32
             planes_cl = ops.planes_to_channels_last(_as_planes_tensor(xy, xz, yz))
             B = xy.shape[0]

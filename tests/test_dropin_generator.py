@@ -110,24 +110,19 @@ def test_patched_decoder_forward_gets_real_planes(monkeypatch):
     assert out["sigma"].shape == (B, 128) and out["rgb"].shape == (B, 128, 3)   # flat, generator.py:604-608
 
 
-def test_patched_decoder_double_backward_on_cpu_keeps_the_reference_path():
-    """N2 on the host: the kernels are CUDA-only, so a CPU caller of the regulariser path (dataset tooling, unit tests of the
-    reference) must still get the reference's own double-differentiable sampler through the replaced forward."""
+def test_patched_decoder_double_backward_fails_loudly_on_cpu():
+    """N2 on the host: like every other op of the package the replaced forward has no CPU path -- a CPU caller of the
+    regulariser path gets a loud NfiError, not a silent fallback."""
+    from nfi_b200._lib import NfiError
     G, rg = _gen("cpu")
     ws = rg.make_ws(1)
-
-    def eik():
-        torch.manual_seed(3)
+    with rg.installed_modules():
         G.train()
         try:
-            return float(G(None, ws, ["sdf_eikonal_loss"], {"freeze_noise": True})["sdf_eikonal_loss"].sum())
+            with pytest.raises(NfiError):
+                G(None, ws, ["sdf_eikonal_loss"], {"freeze_noise": True})
         finally:
             G.eval()
-
-    ref = eik()
-    with rg.installed_modules():
-        got = eik()
-    assert ref > 0 and abs(got - ref) <= 1e-6 * abs(ref)
 
 
 def test_pending_hit_counters_are_per_thread():
