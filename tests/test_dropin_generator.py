@@ -358,6 +358,7 @@ def test_regulariser_path_double_backward_vs_reference(cuda_setup):
         return orig(*a, **k)
 
     ref = run()
+    ref_again = run()          # the reference against itself: its gather backward accumulates with fp32 atomics too
     assert calls["n"] == 0
     ops.decoder_double_backward = counted
     try:
@@ -367,8 +368,13 @@ def test_regulariser_path_double_backward_vs_reference(cuda_setup):
         ops.decoder_double_backward = orig
     assert calls["n"] == 2, "the replaced decoder did not take the double-backward path"
     assert rel_err(got[0].cpu(), ref[0].cpu()) < TOL, (got[0], ref[0])
-    for a, b in zip(got[1], ref[1]):
-        assert rel_err(a.cpu(), b.cpu()) < 5e-4, rel_err(a.cpu(), b.cpu())
+    # Gradient tolerance: 5e-4 plus three times what two runs of the UNPATCHED reference differ by on the same
+    # quantity (both implementations sum tens of thousands of contributions per texel / weight with fp32 atomics in
+    # run-dependent order; measured run to run: 2e-4 .. 6e-4 on the gradient that goes on through StyleGAN2)
+    for a, b, b2 in zip(got[1], ref[1], ref_again[1]):
+        tol = 5e-4 + 3 * rel_err(b2.cpu(), b.cpu())
+        assert rel_err(a.cpu(), b.cpu()) < tol, (rel_err(a.cpu(), b.cpu()), tol)
     assert float(ref[2][0].abs().max()) > 0
-    for a, b in zip(got[2], ref[2]):
-        assert rel_err(a.cpu(), b.cpu()) < 5e-4, rel_err(a.cpu(), b.cpu())
+    for a, b, b2 in zip(got[2], ref[2], ref_again[2]):
+        tol = 5e-4 + 3 * rel_err(b2.cpu(), b.cpu())
+        assert rel_err(a.cpu(), b.cpu()) < tol, (rel_err(a.cpu(), b.cpu()), tol)
